@@ -1,0 +1,238 @@
+"""numpy restatement (fp64) of the reference's lidar rasterisation -- TEST INFRASTRUCTURE.
+
+See oracle/__init__.py for who may import this.  Every function cites the reference
+lines it restates (paths relative to /root/reference/modules/lidar).  The
+restatement is structured differently from the reference on purpose: cells and the
+winner are computed ONCE and made explicit (winner index map, tie mask, counts), so
+parity tests can compare indices / winners / counts bit-exactly and not only the
+rendered images.
+
+Tie rule (the reference leaves it unspecified: unstable `argsort`,
+process/extract_rosbag_lidar.py:65): within a cell the point with the smallest fp64
+`l2_norm` wins; among points whose fp64 `l2_norm` is bit-identical the LOWEST
+original index wins (what a stable sort would give the reference).  `tie_mask`
+marks the cells where the reference's own choice is unspecified.
+"""
+import numpy as np
+
+# ---- process/globals.py:3-13 ------------------------------------------------------
+LIDAR_MAX_HEIGHT = 2
+LIDAR_MIN_HEIGHT = -2
+RES = (1.33, 0.2)                      # (vertical, horizontal) degrees
+VFOV = (-30.67, 10.67)
+RES_RAD = np.array(RES) * (np.pi / 180)
+X_MIN = -360.0 / RES[1] / 2            # -900.0
+Y_MIN = VFOV[0] / RES[0]               # -23.0601...
+X_MAX = int(360.0 / RES[1])            # 1800
+Y_MAX = int(abs(VFOV[0] - VFOV[1]) / RES[0])   # 31
+H = Y_MAX + 1
+W = X_MAX + 1
+
+ERR_ROW_OOB = 1      # row outside [-H, H)   -> numpy IndexError in the reference
+ERR_COL_OOB = 2      # col outside [-W, W)
+ERR_NAN = 4          # NaN cell coordinate (NaN input or rho == 0)
+
+
+class ReferenceIndexError(IndexError):
+    """What the reference raises (numpy fancy-assignment IndexError) for the whole sweep."""
+
+
+def front_view_cells(points):
+    """Per-point cell coordinates, extract_rosbag_lidar.py:26-39,60-61.
+
+    Returns (row, col, rho, err) where row/col are the PRE-flip integer indices after
+    C truncation and numpy negative-index wrap, rho the fp64 l2 norm, err a per-point
+    bitmask (non-zero = the reference would raise IndexError for the sweep)."""
+    p = np.asarray(points, dtype=np.float64)
+    x, y, z = p[:, 0], p[:, 1], p[:, 2]
+    with np.errstate(all="ignore"):
+        rho = np.sqrt(x * x + y * y + z * z)                       # :33
+        xi = np.arctan2(-y, x) / RES_RAD[1] - X_MIN                # :34,38
+        yi = np.arcsin(z / rho) / RES_RAD[0] - Y_MIN               # :35,39
+    err = np.zeros(len(p), dtype=np.int32)
+    nan = np.isnan(xi) | np.isnan(yi)
+    err[nan] |= ERR_NAN
+    xt = np.where(nan, 0.0, np.trunc(xi))                          # astype(int): toward zero :60-61
+    yt = np.where(nan, 0.0, np.trunc(yi))
+    col = xt.astype(np.int64)
+    row = yt.astype(np.int64)
+    err[(row < -H) | (row >= H)] |= ERR_ROW_OOB
+    err[(col < -W) | (col >= W)] |= ERR_COL_OOB
+    row = np.where(row < 0, row + H, row)                          # numpy negative index wrap
+    col = np.where(col < 0, col + W, col)
+    return row, col, rho, err
+
+
+def front_view(points, strict=True):
+    """generate_lidar_2d_front_view(points, cmap=None), extract_rosbag_lidar.py:18-86.
+
+    strict=True  : reference semantics, raises ReferenceIndexError if any point would.
+    strict=False : offending points are dropped (counted in `dropped`).
+    Returns dict with float64 (32,1801) images `distance`, `height`, `intensity`
+    (already flipped, :74), `winner` (int64, -1 = background), `tie_mask`, `dropped`,
+    `err` (OR of the per-point masks)."""
+    p = np.asarray(points, dtype=np.float64)
+    n = len(p)
+    row, col, rho, err = front_view_cells(p)
+    bad = err != 0
+    if strict and bad.any():
+        raise ReferenceIndexError("reference would raise IndexError (err mask %d)" % int(np.bitwise_or.reduce(err)))
+    idx = np.arange(n)[~bad]
+    cell = (row * W + col)[~bad]
+    r = rho[~bad]
+    # nearest wins; equal rho -> lowest index.  Ascending by (rho, idx), assign in reverse
+    # so that the first of the ascending order is written last (:65-71 last-write-wins).
+    order = np.lexsort((idx, r))[::-1]
+    winner = np.full(H * W, -1, dtype=np.int64)
+    winner[cell[order]] = idx[order]
+    # cells whose minimum rho is shared by >1 point: reference's pick is unspecified
+    minr = np.full(H * W, np.inf)
+    np.minimum.at(minr, cell, r)
+    at_min = r == minr[cell]
+    tie = np.bincount(cell[at_min], minlength=H * W) > 1
+    has = winner >= 0
+    w = winner[has]
+    x, y, z, it = p[w, 0], p[w, 1], p[w, 2], p[w, 3]
+    dist = np.zeros(H * W)
+    hgt = np.full(H * W, float(LIDAR_MIN_HEIGHT))                  # :54,62
+    inten = np.zeros(H * W)
+    dist[has] = np.sqrt(x * x + y * y)                             # :32,56
+    hgt[has] = z                                                   # :47
+    inten[has] = it                                                # :45
+    flip = lambda a: a.reshape(H, W)[::-1].copy()                  # :74
+    return {
+        "distance": flip(dist), "height": flip(hgt), "intensity": flip(inten),
+        "winner": flip(winner), "tie_mask": flip(tie),
+        "dropped": int(bad.sum()), "err": int(np.bitwise_or.reduce(err)) if n else 0,
+    }
+
+
+def bev_edges(max_range, res_step):
+    """np.arange(-max_range, max_range, step) restated (birds_eye_view_generator.py:43):
+    n = ceil((stop-start)/step); edge[i] = start + i*delta with
+    delta = (start+step) - start evaluated in fp64 (numpy's arange fill rule)."""
+    start = float(-max_range)
+    stop = float(max_range)
+    step = float(res_step)
+    n = int(np.ceil((stop - start) / step))
+    delta = (start + step) - start
+    return start + np.arange(n, dtype=np.float64) * delta
+
+
+def bev_bin(v, edges):
+    """histogram2d explicit-edge binning (birds_eye_view_generator.py:44): left-closed bins,
+    last bin right-closed, NaN / out-of-range -> -1."""
+    v = np.asarray(v, dtype=np.float64)
+    j = np.searchsorted(edges, v, side="right")
+    j = np.where(v == edges[-1], j - 1, j)
+    b = j - 1
+    ok = (j >= 1) & (j <= len(edges) - 1)
+    return np.where(ok, b, -1)
+
+
+def bev_counts(points, res, max_range=120):
+    """Un-normalised, un-flipped cell counts [x_bin, y_bin] (int64)."""
+    p = np.asarray(points, dtype=np.float64)
+    ex = bev_edges(max_range, res[1])
+    ey = bev_edges(max_range, res[0])
+    bx = bev_bin(p[:, 0], ex)
+    by = bev_bin(p[:, 1], ey)
+    nbx, nby = len(ex) - 1, len(ey) - 1
+    ok = (bx >= 0) & (by >= 0)
+    flat = bx[ok] * nby + by[ok]
+    return np.bincount(flat, minlength=nbx * nby).reshape(nbx, nby).astype(np.int64)
+
+
+def density_lut(nmax=64):
+    """normalize(), birds_eye_view_generator.py:31-37, as a function of the count."""
+    n = np.arange(nmax + 1, dtype=np.float64)
+    with np.errstate(divide="ignore"):
+        v = 255 * np.minimum(np.log(n + 1) / np.log(64), 1)
+    v[0] = 0.0
+    return v
+
+
+def bev_density(points, res, max_range=120):
+    """Pre-colormap float64 image of generate_birds_eye_view (:41-46): counts ->
+    255*min(ln(N+1)/ln 64, 1) -> both axes reversed."""
+    c = bev_counts(points, res, max_range)
+    lut = density_lut(64)
+    d = lut[np.minimum(c, 64)]
+    return d[::-1, ::-1].copy()                                    # :46
+
+
+# ---- MV3D extension channels -- PARITY UNPINNED -------------------
+def bev_height_intensity(points, res, max_range, slice_edges):
+    """Our own definition (no reference code exists): per height slice [lo,hi) the max z
+    per BEV cell (background = slice lo), and the intensity of the highest point per cell
+    over all slices (background 0).  Tie on z -> lowest index.  Flipped like the density."""
+    p = np.asarray(points, dtype=np.float64)
+    ex = bev_edges(max_range, res[1])
+    ey = bev_edges(max_range, res[0])
+    bx = bev_bin(p[:, 0], ex)
+    by = bev_bin(p[:, 1], ey)
+    nbx, nby = len(ex) - 1, len(ey) - 1
+    z = p[:, 2]
+    ok = (bx >= 0) & (by >= 0) & ~np.isnan(z)
+    flat = bx * nby + by
+    m = len(slice_edges) - 1
+    hmaps = np.empty((m, nbx, nby))
+    for s in range(m):
+        lo, hi = slice_edges[s], slice_edges[s + 1]
+        sel = ok & (z >= lo) & (z < hi)
+        h = np.full(nbx * nby, float(lo))
+        np.maximum.at(h, flat[sel], z[sel])
+        hmaps[s] = h.reshape(nbx, nby)
+    sel = ok & (z >= slice_edges[0]) & (z < slice_edges[-1])
+    idx = np.arange(len(p))[sel]
+    order = np.lexsort((-idx, z[sel]))            # ascending z, descending idx; last write = max z, lowest idx
+    top = np.full(nbx * nby, -1, dtype=np.int64)
+    top[flat[sel][order]] = idx[order]
+    inten = np.zeros(nbx * nby)
+    has = top >= 0
+    inten[has] = p[top[has], 3]
+    return hmaps[:, ::-1, ::-1].copy(), inten.reshape(nbx, nby)[::-1, ::-1].copy()
+
+
+# ---- op-for-op port used ONLY as the timed CPU baseline --------------------------------
+def port_front_view_once(points, kind):
+    """One call of lidar_2d_front_view(cmap=None), same numpy call sequence and the same
+    redundant work as the reference (:26-39,60-74), for timing."""
+    x = points[:, 0]; y = points[:, 1]; z = points[:, 2]; r = points[:, 3]
+    d = np.sqrt(x ** 2 + y ** 2)
+    l2 = np.sqrt(x ** 2 + y ** 2 + z ** 2)
+    xi = np.arctan2(-y, x) / RES_RAD[1]
+    yi = np.arcsin(z / l2) / RES_RAD[0]
+    xi -= X_MIN
+    yi -= Y_MIN
+    vals, bg = {"intensity": (r, 0), "height": (z, LIDAR_MIN_HEIGHT), "distance": (d, 0)}[kind]
+    yy = yi.astype(int)
+    xx = xi.astype(int)
+    img = np.ones((H, W)) * bg
+    s = np.flipud(l2.argsort())
+    img[yy[s], xx[s]] = vals[s]
+    return np.flipud(img)
+
+
+def port_generate_lidar_2d_front_view(points):
+    """generate_lidar_2d_front_view: three full passes (:81-83)."""
+    return {k: port_front_view_once(points, k) for k in ("intensity", "distance", "height")}
+
+
+def port_generate_birds_eye_view(points, res, max_range=120, python_loop=True):
+    """generate_birds_eye_view up to the colormap (:42-46).  python_loop=True keeps the
+    reference's per-cell Python `normalize` loop (:31-37); False uses the vectorised
+    equivalent so the cost of that artefact is visible separately."""
+    pts = np.array(points)
+    bins = (np.arange(-max_range, max_range, res[1]), np.arange(-max_range, max_range, res[0]))
+    ch, _, _ = np.histogram2d(pts[:, 0], pts[:, 1], bins=bins)
+    if python_loop:
+        l64 = np.log(64)
+        for i, rowv in enumerate(ch):
+            for j, c in enumerate(rowv):
+                if c > 0:
+                    ch[i][j] = 255 * min(np.log(c + 1) / l64, 1)
+    else:
+        nz = ch > 0
+        ch[nz] = 255 * np.minimum(np.log(ch[nz] + 1) / np.log(64), 1)
+    return np.flipud(np.fliplr(ch))

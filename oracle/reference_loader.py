@@ -1,0 +1,112 @@
+"""Import the reference's own hot-path modules, unmodified, from /root/reference.
+
+TEST INFRASTRUCTURE (see oracle/__init__.py).  Works only where the reference tree
+is mounted (the build container); the GPU box has no /root/reference, so nothing
+that runs there may call this.  Used by tests/golden/make_golden.py to generate the
+committed golden vectors and by the `-m "not gpu"` cross-check of the restatement.
+
+The reference modules import ROS / matplotlib at module scope
+(modules/lidar/process/extract_rosbag_lidar.py:10-16,
+modules/lidar/common/birds_eye_view_generator.py:1-9); none of those is needed by
+the numeric functions, so empty stand-in modules are registered first.  For the BEV
+the only thing matplotlib does is the final colormap (birds_eye_view_generator.py:
+48-53); a stand-in ScalarMappable captures the float array handed to `to_rgba`,
+which is the pre-colormap density image the parity contract is written against.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+REFERENCE_ROOT = os.environ.get("SFPE_REFERENCE_ROOT", "/root/reference")
+_LIDAR = os.path.join(REFERENCE_ROOT, "modules", "lidar")
+
+_cache = {}
+
+
+def available():
+    return os.path.isfile(os.path.join(_LIDAR, "process", "extract_rosbag_lidar.py"))
+
+
+class _Capture:
+    """Holds the last array passed to the stand-in colormap."""
+    last = None
+
+
+def _install_stubs():
+    def mod(name):
+        m = sys.modules.get(name)
+        if m is None:
+            m = types.ModuleType(name)
+            sys.modules[name] = m
+        return m
+
+    mod("rosbag")
+    sm = mod("sensor_msgs")
+    sm.point_cloud2 = mod("sensor_msgs.point_cloud2")
+    mpl = mod("matplotlib")
+    if not hasattr(mpl, "use"):
+        mpl.use = lambda *a, **k: None
+    for sub in ("cm", "colors", "image", "pyplot"):
+        setattr(mpl, sub, mod("matplotlib." + sub))
+
+    class Normalize:
+        def __init__(self, vmin=None, vmax=None):
+            self.vmin, self.vmax = vmin, vmax
+
+    class ScalarMappable:
+        def __init__(self, cmap=None, norm=None):
+            self.cmap, self.norm = cmap, norm
+
+        def to_rgba(self, x, bytes=False, norm=True):
+            import numpy as np
+            _Capture.last = np.array(x, copy=True)
+            return np.zeros(x.shape + (4,), dtype=np.uint8)
+
+    if not hasattr(mpl.colors, "Normalize"):
+        mpl.colors.Normalize = Normalize
+    if not hasattr(mpl.cm, "ScalarMappable"):
+        mpl.cm.ScalarMappable = ScalarMappable
+
+
+def _load(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def load():
+    """Returns (extract_rosbag_lidar module, birds_eye_view_generator module, globals module)."""
+    if "mods" in _cache:
+        return _cache["mods"]
+    if not available():
+        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+    _install_stubs()
+    proc = os.path.join(_LIDAR, "process")
+    # `import globals` (py2-style sibling import) must resolve to process/globals.py
+    sys.path.insert(0, proc)
+    try:
+        sys.modules.pop("globals", None)
+        erl = _load("_ref_extract_rosbag_lidar", os.path.join(proc, "extract_rosbag_lidar.py"))
+        bev = _load("_ref_birds_eye_view_generator",
+                    os.path.join(_LIDAR, "common", "birds_eye_view_generator.py"))
+        glb = sys.modules["globals"]
+    finally:
+        sys.path.remove(proc)
+    _cache["mods"] = (erl, bev, glb)
+    return _cache["mods"]
+
+
+def front_view(points):
+    """reference generate_lidar_2d_front_view(points, cmap=None) -> dict of float64 (32,1801)."""
+    erl, _, _ = load()
+    return erl.generate_lidar_2d_front_view(points, cmap=None)
+
+
+def bev_density(points, res, max_range=120):
+    """Pre-colormap float64 density image of reference generate_birds_eye_view."""
+    _, bev, _ = load()
+    _Capture.last = None
+    bev.generate_birds_eye_view(points, 0, res, max_range=max_range, cmap="gray")
+    return _Capture.last

@@ -1,0 +1,76 @@
+"""Seeded synthetic Velodyne-shaped sweeps (SURVEY.md 8d "Synthetic inputs").
+
+Host-side data generation only -- there is no dataset on the box.  A sweep is
+`beams x n_az` returns in firing order (azimuth-major, beam-minor): each ray hits
+either the ground plane z = -1.7 m or an "object" at U(2, 80) m, whichever is
+nearer.  All coordinates are rounded to float32, which is what a PointCloud2 blob
+carries (reference: team_sf_rosnode/scripts/lidar_predict.py:64-65 decodes float32
+fields into a float64 array).  Elevations stay inside the reference's safe band
+(process/globals.py:7 VFOV) so the reference neither wraps nor raises.
+"""
+import numpy as np
+
+# name -> (beams, n_az, el_lo_deg, el_hi_deg)
+SENSORS = {
+    "hdl32": (32, 2048, -30.67, 10.67),      # 65 536 pts
+    "hdl64": (64, 1875, -24.9, 2.0),         # 120 000 pts
+    "vls128": (128, 1953, -25.0, 10.5),      # 249 984 pts
+}
+
+
+def make_sweep(sensor="hdl32", seed=0, dropout=0.0, shuffle=False, near_heavy=False,
+               beams=None, n_az=None):
+    """Returns a C-contiguous float32 (N, 4) array [x, y, z, intensity]."""
+    b, na, el_lo, el_hi = SENSORS[sensor]
+    if beams is not None:
+        b = beams
+    if n_az is not None:
+        na = n_az
+    rng = np.random.default_rng(seed)
+    el = np.deg2rad(np.linspace(el_lo, el_hi, b))
+    # keep the extreme beams strictly inside the band after float32 rounding
+    el = np.clip(el, np.deg2rad(el_lo) + 1e-4, np.deg2rad(el_hi) - 1e-4)
+    az = np.linspace(-np.pi, np.pi, na, endpoint=False)
+    az = az + np.deg2rad(rng.uniform(-0.02, 0.02, size=na))
+    az = np.clip(az, -np.pi + 1e-6, np.pi - 1e-6)
+    A, E = np.meshgrid(az, el, indexing="ij")            # (n_az, beams): firing order
+    A = A.ravel()
+    E = E.ravel()
+    n = A.size
+    with np.errstate(divide="ignore"):
+        ground = np.where(E < 0, 1.7 / np.sin(-E), np.inf)
+    if near_heavy:                                        # C5: 60 % of object returns < 15 m
+        near = rng.random(n) < 0.6
+        obj = np.where(near, rng.uniform(2.0, 15.0, n), rng.uniform(15.0, 80.0, n))
+    else:
+        obj = rng.uniform(2.0, 80.0, n)
+    has_obj = (rng.random(n) < 0.35) | (ground > 100.0)
+    rho = np.where(has_obj, np.minimum(obj, ground), ground)
+    ce = np.cos(E)
+    pts = np.empty((n, 4), dtype=np.float32)
+    pts[:, 0] = rho * ce * np.cos(A)
+    pts[:, 1] = rho * ce * np.sin(A)
+    pts[:, 2] = rho * np.sin(E)
+    pts[:, 3] = rng.uniform(0.0, 255.0, n)
+    if dropout > 0:
+        pts = pts[rng.random(n) >= dropout]
+    if shuffle:
+        pts = pts[rng.permutation(len(pts))]
+    return np.ascontiguousarray(pts)
+
+
+def make_batch(n_sweeps, sensor="hdl32", seed0=0, **kw):
+    """Concatenated points (sum N, 4) float32 and int64 frame offsets (n_sweeps + 1)."""
+    sweeps = [make_sweep(sensor, seed0 + i, **kw) for i in range(n_sweeps)]
+    offs = np.zeros(n_sweeps + 1, dtype=np.int64)
+    offs[1:] = np.cumsum([len(s) for s in sweeps])
+    return np.concatenate(sweeps, axis=0), offs
+
+
+def as_reference_array(points_f32):
+    """(N,5) float64 [x,y,z,intensity,ring] -- the layout the reference's callers hand to the
+    projection (np.array(list(read_points(msg)))); ring is ignored by the hot path."""
+    n = len(points_f32)
+    out = np.zeros((n, 5), dtype=np.float64)
+    out[:, :4] = points_f32
+    return out

@@ -1,0 +1,84 @@
+"""The numpy restatement (oracle/lidar_oracle.py) against the committed outputs of the
+reference's own functions (tests/golden/, made by tests/golden/make_golden.py).
+Bit-exact: the oracle computes in fp64 with the same numpy primitives."""
+import numpy as np
+import pytest
+
+from conftest import golden
+from oracle import lidar_oracle as lo
+from oracle import reference_loader as rl
+
+FRONT = ["hdl32_seed0", "hdl32_seed1_shuffled_dropout", "hdl64_seed2", "vls128_seed3_near",
+         "small_seed4", "edges"]
+
+
+def _P(g):
+    p = np.zeros((len(g["points"]), 5))
+    p[:, :4] = g["points"]
+    return p
+
+
+@pytest.mark.parametrize("name", FRONT)
+def test_front_view_matches_reference_golden(name):
+    g = golden(name)
+    o = lo.front_view(_P(g))
+    for k in ("distance", "height", "intensity"):
+        a, b = g[k], o[k]
+        # cells where the reference's own winner is unspecified (exact fp64 range ties) are excluded
+        ok = ~o["tie_mask"]
+        assert np.array_equal(a[ok], b[ok]), k
+    assert o["winner"].shape == (32, 1801)
+
+
+@pytest.mark.parametrize("name", FRONT + ["bev_edges"])
+def test_bev_density_matches_reference_golden(name):
+    g = golden(name)
+    for key in [k for k in g.files if k.startswith("bev_")]:
+        r = float(key[4:])
+        d = lo.bev_density(_P(g), (r, r), 120)
+        assert d.shape == g[key].shape
+        assert np.array_equal(d, g[key]), key
+
+
+@pytest.mark.parametrize("name", ["raises_high_elevation", "raises_origin", "raises_nan", "raises_low_elevation"])
+def test_reference_index_error_cases(name):
+    g = golden(name)
+    with pytest.raises(IndexError):
+        lo.front_view(_P(g), strict=True)
+    o = lo.front_view(_P(g), strict=False)
+    assert o["dropped"] == 1 and o["err"] != 0
+
+
+def test_edges_rule():
+    for R, res in [(120, 0.2), (120, 2), (120, 0.05), (100, 0.25), (120, 0.1)]:
+        assert np.array_equal(lo.bev_edges(R, res), np.arange(-R, R, res).astype(np.float64))
+
+
+def test_cell_convention_landmarks():
+    # col 900 straight ahead, y>0 -> smaller column, el=0 -> output row 8
+    pts = np.array([[10, 0, 0, 1], [0, 10, 0, 2], [0, -10, 0, 3], [-10, 1e-9, 0, 4], [-10, -0.0, 0, 5]], float)
+    w = lo.front_view(pts)["winner"]
+    rows, cols = np.nonzero(w >= 0)
+    got = {int(w[r, c]): (int(r), int(c)) for r, c in zip(rows, cols)}
+    assert got[0] == (8, 900) and got[1] == (8, 450) and got[2] == (8, 1350)
+    assert got[3] == (8, 0) and got[4] == (8, 1800)
+
+
+def test_density_lut_saturates():
+    lut = lo.density_lut(64)
+    assert lut[0] == 0 and lut[63] == 255.0 and lut[64] == 255.0 and 0 < lut[1] < lut[2]
+
+
+@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted (GPU box)")
+def test_oracle_equals_live_reference(synth):
+    p = synth.make_sweep("hdl32", seed=11, n_az=300, shuffle=True)
+    P = synth.as_reference_array(p)
+    ref = rl.front_view(P)
+    o = lo.front_view(P)
+    for k in ("distance", "height", "intensity"):
+        assert np.array_equal(ref[k + "_float"], o[k])
+    assert np.array_equal(rl.bev_density(P, (0.5, 0.5)), lo.bev_density(P, (0.5, 0.5)))
+    port = lo.port_generate_lidar_2d_front_view(P)
+    for k in port:
+        assert np.array_equal(port[k], ref[k + "_float"])
+    assert np.array_equal(lo.port_generate_birds_eye_view(P, (2, 2)), rl.bev_density(P, (2, 2)))
