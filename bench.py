@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""bench.py -- lidar sweeps/s of the BEV + range-scan projection (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): a batch of 1024 synthetic HDL-32E sweeps (32 x 2048 =
+65 536 points each, float32 x,y,z,intensity), reference grid (32 x 1801 range scan, +-120 m BEV
+at 0.2 m -> 1199 x 1199), one B200.  One "step" = one pass of the hot path over the whole batch.
+Each rank owns its own batch (frame sharding, no collective): weak scaling.
+
+  python bench.py [--gpus N --steps K --warmup W]            our CUDA path
+  python bench.py --impl reference [...]                      the reference's numpy algorithm on host cores
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "sensor-fusion-pose-estimation-challenge_b200"
+
+H, W = 32, 1801
+
+
+def algorithmic_bytes(n_pts, nbx, nby, c_bev=1):
+    """float4 read once + fp32 range tensor written once + fp32 BEV written once."""
+    return 16 * n_pts + 4 * 3 * H * W + 4 * c_bev * nbx * nby
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------ CPU baseline
+def _cpu_worker(args):
+    """Times the reference's numpy algorithm (oracle port, op for op) on one host core."""
+    seeds, sensor, bev_res = args
+    synth = importlib.import_module(PKG + ".synth") if False else None  # product package needs the .so; avoid
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("synth", os.path.join(ROOT, PKG, "synth.py"))
+    synth = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(synth)
+    from oracle import lidar_oracle as lo
+    pts = [synth.as_reference_array(synth.make_sweep(sensor, s)) for s in seeds]
+    t0 = time.perf_counter()
+    for P in pts:
+        lo.port_generate_lidar_2d_front_view(P)
+        lo.port_generate_birds_eye_view(P, bev_res, 120, python_loop=True)
+    return time.perf_counter() - t0
+
+
+def cpu_reference_pass(n_sweeps, sensor, bev_res, cores, seed0=0):
+    """One bounded sample: n_sweeps sweeps spread over `cores` worker processes.  Returns seconds (wall)."""
+    import multiprocessing as mp
+    chunks = [list(range(seed0 + i, seed0 + n_sweeps, cores)) for i in range(cores)]
+    chunks = [c for c in chunks if c]
+    ctx = mp.get_context("spawn")
+    with ctx.Pool(len(chunks)) as pool:
+        pool.map(_cpu_worker, [([c[0]], sensor, bev_res) for c in chunks])     # warm the workers (imports)
+        t0 = time.perf_counter()
+        pool.map(_cpu_worker, [(c, sensor, bev_res) for c in chunks])
+        return time.perf_counter() - t0
+
+
+def run_reference(a):
+    """--impl reference: the reference's own CPU algorithm (oracle port; the reference is Python and
+    cannot travel to the GPU box) on all host cores, same metric / config."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    per_step = max(cores, 8)
+    times = []
+    for i in range(a.warmup + a.steps):
+        dt = cpu_reference_pass(per_step, a.sensor, (a.bev_res, a.bev_res), cores, seed0=i * per_step)
+        if i >= a.warmup:
+            times.append(dt)
+    total = sum(times)
+    val = per_step * len(times) / total
+    cfg = workload_config(a)
+    line = {
+        "impl": "reference", "metric": "lidar sweeps/s (BEV+range projection)", "value": val, "unit": "sweeps/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * total / len(times),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": cfg,
+        "cpu_baseline": {"value": val, "unit": "sweeps/s", "cores": cores, "kind": "port",
+                         "sample": "%d sweeps per step x %d steps, numpy port of the reference "
+                                   "(3x front view + histogram2d + per-cell python normalize loop)" % (per_step, len(times))},
+        "e2e": {"value": val, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def workload_config(a):
+    return {"workload": "batch of %d synthetic %s sweeps (%d pts each), range scan 32x1801x3 + BEV density "
+                        "+-120 m @ %g m" % (a.sweeps, a.sensor, a.n_pts, a.bev_res),
+            "sweeps_per_gpu": a.sweeps, "points_per_sweep": a.n_pts, "bev_res_m": a.bev_res,
+            "l2_policy": "inputs (%.2f GB) and outputs larger than the 126 MB L2; no flush needed" % (a.sweeps * a.n_pts * 16 / 1e9),
+            "parallelism": "frame sharding, %d rank(s), no collective" % a.gpus}
+
+
+# ------------------------------------------------------------------------------ GPU arm
+def run_ours(a):
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module(PKG)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    # synthetic batch: distinct seeds per rank; generated on the host, resident in HBM before timing
+    pool = min(a.sweeps, a.distinct)
+    host = np.concatenate([pkg.synth.make_sweep(a.sensor, seed=rank * a.sweeps + i) for i in range(pool)])
+    reps = (a.sweeps + pool - 1) // pool
+    host_all = np.concatenate([host] * reps)[: a.sweeps * a.n_pts] if reps > 1 else host
+    pin_in = torch.from_numpy(host_all).pin_memory()
+    d_pts = pin_in.to(dev, non_blocking=True)
+    pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path)
+    out = pr.alloc_outputs(a.sweeps)
+    torch.cuda.synchronize()
+
+    def step():
+        pr.project(d_pts, n_frames=a.sweeps, uniform_n=a.n_pts, out=out)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    l0 = pr.launch_count
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps + 1)]
+    barrier()
+    ev[0].record()
+    for i in range(a.steps):
+        step()
+        ev[i + 1].record()
+    barrier()
+    launches = pr.launch_count - l0
+    total_ms = ev[0].elapsed_time(ev[-1])
+    step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(a.steps)]
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+
+    # ---- e2e: same metric through the host-buffer API, H2D + D2H inside the timed region
+    e2e = None
+    if not a.no_e2e:
+        e2e = run_e2e(a, pkg, pr, pin_in, dev, world)
+
+    status_bad = int((out["status"] != 0).sum().item())
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        bytes_sweep = algorithmic_bytes(a.n_pts, pr.nbx, pr.nby)
+        med_ms = float(np.median(step_ms))
+        achieved = a.sweeps * bytes_sweep / (med_ms * 1e-3) / 1e9
+        value = world * a.sweeps * a.steps / (total_ms * 1e-3)
+        line = {
+            "metric": "lidar sweeps/s (BEV+range projection)", "value": value, "unit": "sweeps/s",
+            "points_per_s": value * a.n_pts,
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": total_ms / a.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(a),
+            "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_sweep": bytes_sweep, "launch_ms": med_ms,
+                         "kernel": "fused k_fused_sweep (one launch per step)" if pr.last_path == "fused"
+                         else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
+            "clocks": clocks,
+        }
+        if e2e is not None:
+            line["e2e"] = e2e
+        if not a.no_cpu and world == 1:
+            cores = os.cpu_count() or 1
+            n = max(cores, 8) * 2
+            dt = cpu_reference_pass(n, a.sensor, (a.bev_res, a.bev_res), cores)
+            line["cpu_baseline"] = {"value": n / dt, "unit": "sweeps/s", "cores": cores, "kind": "port",
+                                    "sample": "%d sweeps of the same workload, numpy port of the reference in %d "
+                                              "processes (%.1f s)" % (n, cores, dt)}
+        print(json.dumps(line))
+    pr.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(a, pkg, pr, pin_in, dev, world):
+    """Host pinned in -> H2D -> kernels -> D2H of every output image, pipelined over chunks on 3 streams."""
+    import torch
+    import torch.distributed as dist
+    hb = pkg.HostBatchPipeline(pr, a.sweeps, a.n_pts, chunk=a.e2e_chunk)
+    steps = max(2, min(a.steps, 5))
+    hb.run(pin_in)            # warm-up (also faults the pinned output pages in)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        hb.run(pin_in)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    return {"value": world * a.sweeps * steps / dt, "unit": "sweeps/s", "steps": steps,
+            "h2d_bytes_per_step": int(hb.h2d_bytes), "d2h_bytes_per_step": int(hb.d2h_bytes),
+            "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; PCIe bound" % hb.chunk}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--sweeps", type=int, default=1024)
+    ap.add_argument("--sensor", default="hdl32")
+    ap.add_argument("--bev-res", type=float, default=0.2)
+    ap.add_argument("--distinct", type=int, default=1024, help="distinct synthetic sweeps generated (rest repeat)")
+    ap.add_argument("--path", type=int, default=0, help="0 auto, 1 generic, 2 fused")
+    ap.add_argument("--e2e-chunk", type=int, default=32)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    a = ap.parse_args()
+    a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
+    sens = {"hdl32": 65536, "hdl64": 120000, "vls128": 249984}
+    a.n_pts = sens[a.sensor]
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+
+
+if __name__ == "__main__":
+    main()

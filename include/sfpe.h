@@ -1,0 +1,184 @@
+/* sfpe.h -- C ABI of libsfpe.so: B200 (sm_100a) lidar rasterisation.
+ *
+ * Drop-in boundary for ONE hot path of J-Rojas/Sensor-Fusion-Pose-Estimation-Challenge:
+ * the projection of a Velodyne sweep into (a) the 360-degree cylindrical range scan and
+ * (b) the bird's-eye-view density map.  The reference has no FFI layer; it calls plain
+ * numpy functions.  Each entry point below names the reference function it replaces
+ * (paths relative to modules/lidar/ of the reference):
+ *
+ *   sfpe_project_batch        process/extract_rosbag_lidar.py:18-86  (lidar_2d_front_view x3 =
+ *                             generate_lidar_2d_front_view) and
+ *                             common/birds_eye_view_generator.py:31-54 (normalize +
+ *                             generate_birds_eye_view), for a batch of independent sweeps
+ *   sfpe_project_sweep_host   the same, one sweep from/to HOST buffers -- the call made by
+ *                             train/predict.py:335-341 (predict_point_cloud) behind
+ *                             team_sf_rosnode/scripts/lidar_predict.py:60-70
+ *   sfpe_decode_pointcloud2   sensor_msgs.point_cloud2.read_points + np.array(list(..)) at
+ *                             team_sf_rosnode/scripts/lidar_predict.py:64-65,
+ *                             process/extract_rosbag.py:165-166, train/predict.py:373-374
+ *   sfpe_params defaults      process/globals.py:3-13 (RES, VFOV, LIDAR_MIN_HEIGHT, ...)
+ *
+ * Conventions: every function returns 0 (SFPE_OK) or a negative sfpe_status; nothing throws
+ * across the ABI.  All buffers are owned by the caller; the library owns only scratch
+ * inside the ctx.  "device" pointers are CUDA device pointers of the ctx's device.
+ * `stream` is a cudaStream_t passed as void* (NULL = the ctx's own stream).  One ctx per
+ * device per thread; a ctx is not re-entrant.  There is NO CPU fallback: without a CUDA
+ * device sfpe_create fails with SFPE_ERR_CUDA.
+ */
+#ifndef SFPE_H_
+#define SFPE_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SFPE_API __attribute__((visibility("default")))
+#else
+#define SFPE_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SFPE_ABI_VERSION 1
+#define SFPE_MAX_SLICES 8
+
+typedef enum {
+  SFPE_OK = 0,
+  SFPE_ERR_INVALID_ARG = -1,
+  SFPE_ERR_CUDA = -2,
+  SFPE_ERR_UNSUPPORTED = -3,
+  SFPE_ERR_NOMEM = -4
+} sfpe_status;
+
+/* element types of point fields and float outputs */
+enum { SFPE_F32 = 0, SFPE_F64 = 1 };
+
+/* range-scan tensor layouts.  Channel order is (distance, height, intensity), the order
+ * train/predict.py:339-341 and train/loader.py:197-207 feed the network. */
+enum {
+  SFPE_RANGE_CHW = 0, /* [frame][3][H][W]  -- three planar images, like the reference dict */
+  SFPE_RANGE_HWC = 1  /* [frame][H][W][3]  -- the (32,1801,3) network input */
+};
+
+/* per-frame status bits: a non-zero value means the reference would have raised
+ * IndexError for that sweep (extract_rosbag_lidar.py:71 fancy assignment). */
+enum {
+  SFPE_FRAME_ROW_OOB = 1, /* elevation cell outside [-H, H)  */
+  SFPE_FRAME_COL_OOB = 2, /* azimuth cell outside [-W, W)    */
+  SFPE_FRAME_NAN = 4      /* NaN cell coordinate (NaN input, or the origin) */
+};
+
+/* Grid / extent parameters.  sfpe_default_params() fills the reference's values. */
+typedef struct {
+  double res_v_deg;    /* RES[0]  = 1.33   process/globals.py:6 */
+  double res_h_deg;    /* RES[1]  = 0.2                         */
+  double vfov_lo_deg;  /* VFOV[0] = -30.67 process/globals.py:7 */
+  double vfov_hi_deg;  /* VFOV[1] = 10.67                       */
+  double height_bg;    /* LIDAR_MIN_HEIGHT = -2: background of the height image */
+  double bev_range;    /* max_range = 120  birds_eye_view_generator.py:41 */
+  double bev_res_x;    /* res[1]: step of the x (first histogram axis) bin edges */
+  double bev_res_y;    /* res[0]: step of the y bin edges */
+  int32_t enable_range; /* compute the range scan */
+  int32_t enable_bev;   /* compute the BEV density */
+  /* extensions, default off (parity unpinned) */
+  int32_t use_extrinsic; /* apply p' = float32(M[3x4] * (x,y,z,1)) before projecting */
+  int32_t n_slices;      /* >0: MV3D height-slice maps + intensity-of-highest-point */
+  double extrinsic[12];
+  double slice_edges[SFPE_MAX_SLICES + 1];
+  /* tuning / test hooks */
+  int32_t key_prefix_bits; /* 0 = auto.  Bits of the fp64 range kept in the packed winner key;
+                              small values force the exact-compare slow path (tests). */
+  int32_t path;            /* 0 = auto, 1 = generic global-scratch kernels, 2 = fused cluster kernel */
+  int32_t reserved[6];
+} sfpe_params;
+
+/* Where the points of a batch live (device memory).  Point p of the batch is at
+ * data + p*stride_bytes; its fields at the given byte offsets.  The packed hot-path
+ * layout is float32 x,y,z,intensity: stride 16, offsets 0,4,8,12, 16-byte aligned. */
+typedef struct {
+  const void* data;
+  int64_t stride_bytes;
+  int32_t dtype; /* SFPE_F32 or SFPE_F64 */
+  int32_t off_x, off_y, off_z, off_i;
+  int32_t reserved;
+} sfpe_points;
+
+/* Output buffers (device).  Any pointer may be NULL = not wanted. */
+typedef struct {
+  void* range;            /* n_frames * 3*H*W elements of range_dtype, layout range_layout */
+  int32_t range_dtype;    /* SFPE_F32 / SFPE_F64 */
+  int32_t range_layout;   /* SFPE_RANGE_CHW / SFPE_RANGE_HWC */
+  int32_t* range_winner;  /* [frame][H][W] index (within the frame) of the winning point, -1 = none */
+  void* bev;              /* [frame][nbx][nby] density 255*min(ln(N+1)/ln64,1), both axes reversed */
+  int32_t bev_dtype;      /* SFPE_F32 / SFPE_F64 */
+  int32_t reserved0;
+  uint32_t* bev_counts;   /* [frame][nbx][nby] raw counts, NOT reversed ([x_bin][y_bin]) */
+  float* bev_height;      /* [frame][n_slices][nbx][nby], reversed like bev (extension) */
+  float* bev_intensity;   /* [frame][nbx][nby] (extension) */
+  int32_t* status;        /* [frame] OR of SFPE_FRAME_* bits */
+  int32_t* dropped;       /* [frame] number of points that hit a status bit (not rasterised) */
+  void* reserved[4];
+} sfpe_outputs;
+
+typedef struct sfpe_ctx sfpe_ctx;
+
+SFPE_API int sfpe_abi_version(void);
+SFPE_API const char* sfpe_strerror(int status);
+SFPE_API void sfpe_default_params(sfpe_params* p);
+
+/* Derived grid sizes for a parameter set (host arithmetic only; mirrors process/globals.py:9-13
+ * and np.arange's length rule): H = Y_MAX+1, W = X_MAX+1, nbx/nby = BEV bins per axis. */
+SFPE_API int sfpe_grid_dims(const sfpe_params* p, int32_t* H, int32_t* W, int32_t* nbx, int32_t* nby);
+
+SFPE_API int sfpe_create(int device, const sfpe_params* p, sfpe_ctx** out);
+SFPE_API void sfpe_destroy(sfpe_ctx* ctx);
+SFPE_API const char* sfpe_last_error(const sfpe_ctx* ctx); /* text of the last CUDA failure */
+
+/* Rasterise n_frames independent sweeps.  Frame f owns points
+ * [frame_offsets[f], frame_offsets[f+1]) of `pts` (d_frame_offsets: DEVICE int64[n_frames+1]);
+ * with d_frame_offsets == NULL every frame has exactly uniform_n points.  max_n bounds the
+ * points of any frame (grid sizing; must be < 2^31).  Asynchronous on `stream`. */
+SFPE_API int sfpe_project_batch(sfpe_ctx* ctx, const sfpe_points* pts, const int64_t* d_frame_offsets,
+                       int64_t uniform_n, int64_t max_n, int32_t n_frames,
+                       const sfpe_outputs* out, void* stream);
+
+/* One sweep, HOST in / HOST out (pinned or pageable): H2D, kernels, D2H, synchronised.
+ * host_points has n points in the layout `layout` describes (layout->data ignored).
+ * h_range: 3*H*W elements (range_dtype/range_layout), h_bev: nbx*nby elements, h_winner:
+ * H*W int32 -- any may be NULL.  *frame_status receives the SFPE_FRAME_* mask. */
+SFPE_API int sfpe_project_sweep_host(sfpe_ctx* ctx, const void* host_points, const sfpe_points* layout,
+                            int64_t n, void* h_range, int32_t range_dtype, int32_t range_layout,
+                            int32_t* h_winner, void* h_bev, int32_t bev_dtype,
+                            int32_t* frame_status, int32_t* frame_dropped);
+
+/* PointCloud2 `data` blob (device) -> packed float32 x,y,z,intensity (device, 16 B/point).
+ * n = width*height points of point_step bytes; offsets/dtypes of the 4 fields as in
+ * msg.fields (datatype 7 = FLOAT32 -> SFPE_F32, 8 = FLOAT64 -> SFPE_F64). */
+SFPE_API int sfpe_decode_pointcloud2(sfpe_ctx* ctx, const void* d_blob, int64_t n, int32_t point_step,
+                            int32_t off_x, int32_t off_y, int32_t off_z, int32_t off_i,
+                            int32_t dtype, float* d_xyzi, void* stream);
+
+/* Colormap stage (extract_rosbag_lidar.py:41,49-53,75; birds_eye_view_generator.py:48-53:
+ * matplotlib ScalarMappable.to_rgba(img, bytes=True)[:,:,0:3]).  PARITY UNPINNED: the byte
+ * arithmetic lives in matplotlib, which the reference neither vendors nor pins.  Definition
+ * used here: t=(v-vmin)/(vmax-vmin) (autoscale: vmin/vmax = finite min/max of the image; a
+ * flat image maps to t=0), index=min(trunc(t*256),255) clamped to [0,255], NaN -> (0,0,0);
+ * SFPE_CMAP_GRAY: r=g=b=index; SFPE_CMAP_JET: matplotlib's piecewise-linear "jet" segments
+ * sampled at index/255, byte = trunc(255*c).  d_img: n elements of `dtype`; d_rgb: 3*n bytes. */
+enum { SFPE_CMAP_GRAY = 0, SFPE_CMAP_JET = 1 };
+SFPE_API int sfpe_colormap(sfpe_ctx* ctx, const void* d_img, int32_t dtype, int64_t n, int32_t cmap,
+                  int32_t autoscale, double vmin, double vmax, uint8_t* d_rgb, void* stream);
+/* same, HOST in / HOST out, synchronised */
+SFPE_API int sfpe_colormap_host(sfpe_ctx* ctx, const void* h_img, int32_t dtype, int64_t n, int32_t cmap,
+                       int32_t autoscale, double vmin, double vmax, uint8_t* h_rgb);
+
+/* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
+SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);
+/* Name of the code path the last sfpe_project_batch took ("generic", "fused"). */
+SFPE_API const char* sfpe_last_path(const sfpe_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SFPE_H_ */

@@ -1,0 +1,63 @@
+// Internal host/device interface between the C-ABI translation unit and the kernel files.
+#pragma once
+#include "sfpe_common.cuh"
+
+namespace sfpe {
+
+struct FrameSet {
+  const long long* offsets;  // device int64[n_frames+1] or nullptr
+  long long uniform_n;       // used when offsets == nullptr
+  int frame0;                // first frame of this chunk (global frame index)
+  int n_frames;              // frames in this chunk
+};
+
+__device__ __forceinline__ void frame_span(const FrameSet& fs, int f, long long& base, long long& n) {
+  if (fs.offsets) {
+    base = fs.offsets[f];
+    n = fs.offsets[f + 1] - base;
+  } else {
+    base = (long long)f * fs.uniform_n;
+    n = fs.uniform_n;
+  }
+}
+
+struct DevOut {
+  void* range;
+  int range_dtype, range_layout;
+  int* range_winner;
+  void* bev;
+  int bev_dtype;
+  unsigned* bev_counts;
+  float* bev_height;
+  float* bev_intensity;
+  int* status;
+  int* dropped;
+};
+
+// Scratch owned by the ctx, sized for `chunk` frames.
+struct Scratch {
+  unsigned long long* keys;  // [chunk][H*W]   packed winner keys, KEY_EMPTY when idle
+  unsigned* counts;          // [chunk][nbx*nby] BEV counts, 0 when idle
+  unsigned long long* top;   // [chunk][nbx*nby] extension: highest-point key, 0 when idle
+  unsigned* slice_max;       // [chunk][n_slices][nbx*nby] extension: ordered max z, 0 when idle
+  const double* lut;         // [65] density LUT (device computed)
+};
+
+// generic (global-scratch) path -- sfpe_generic.cu
+cudaError_t launch_fill_scratch(const DevGrid& g, const Scratch& s, int chunk, cudaStream_t st, long long* launches);
+cudaError_t launch_density_lut(double* d_lut, cudaStream_t st, long long* launches);
+cudaError_t launch_generic_chunk(const DevGrid& g, const PointSrc& src, const FrameSet& fs, long long max_n,
+                                 const Scratch& s, const DevOut& out, cudaStream_t st, long long* launches);
+cudaError_t launch_decode_pc2(const void* blob, long long n, int step, int ox, int oy, int oz, int oi, int dtype,
+                              float* out, cudaStream_t st, long long* launches);
+
+// mm: device double[2] scratch {min,max} (only touched when autoscale)
+cudaError_t launch_colormap(const void* img, int dtype, long long n, int cmap, int autoscale, double vmin, double vmax,
+                            unsigned long long* mm, unsigned char* rgb, cudaStream_t st, long long* launches);
+
+// fused cluster path -- sfpe_fused.cu
+bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, int device);
+cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, long long max_n,
+                         const Scratch& s, const DevOut& out, int device, cudaStream_t st, long long* launches);
+
+}  // namespace sfpe

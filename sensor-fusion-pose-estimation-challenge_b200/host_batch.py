@@ -1,0 +1,65 @@
+"""Host-buffer batch entry: pinned host sweeps in, pinned host images out.
+
+This is the "reference-facing" way to use the library for many sweeps (what
+extract_rosbag.py:162-187 does one message at a time on the CPU): the batch is cut into
+chunks that flow through three CUDA streams -- H2D copy, kernels, D2H copy -- with two
+device slots, so both PCIe directions and the SMs work concurrently.  torch is used for
+pinned/device memory, streams and events only.
+"""
+from .projector import LidarProjector
+
+
+class HostBatchPipeline:
+    def __init__(self, projector: LidarProjector, n_frames, points_per_frame, chunk=32):
+        import torch
+        self.torch = torch
+        self.pr = projector
+        self.n_frames, self.n = int(n_frames), int(points_per_frame)
+        self.chunk = max(1, min(int(chunk), self.n_frames))
+        dev = torch.device("cuda", projector.device)
+        self.dev = dev
+        self.s_in, self.s_k, self.s_out = (torch.cuda.Stream(dev) for _ in range(3))
+        self.d_in = [torch.empty((self.chunk * self.n, 4), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.d_out = [projector.alloc_outputs(self.chunk) for _ in range(2)]
+        p = projector
+        self.h_range = torch.empty((self.n_frames, p.H, p.W, 3), dtype=torch.float32).pin_memory() \
+            if p.params.enable_range else None
+        self.h_bev = torch.empty((self.n_frames, p.nbx, p.nby), dtype=torch.float32).pin_memory() \
+            if p.params.enable_bev else None
+        self.h_status = torch.empty((self.n_frames,), dtype=torch.int32).pin_memory()
+        self.h2d_bytes = self.n_frames * self.n * 16
+        self.d2h_bytes = (self.h_range.numel() * 4 if self.h_range is not None else 0) + \
+                         (self.h_bev.numel() * 4 if self.h_bev is not None else 0) + self.n_frames * 4
+
+    def run(self, pinned_points):
+        """pinned_points: pinned CPU float32 tensor (n_frames*n, 4).  Asynchronous; results are in
+        self.h_range / self.h_bev / self.h_status after torch.cuda.synchronize()."""
+        torch = self.torch
+        ev_in = [None, None]; ev_k = [None, None]; ev_out = [None, None]
+        n_chunks = (self.n_frames + self.chunk - 1) // self.chunk
+        for c in range(n_chunks):
+            s = c & 1
+            f0 = c * self.chunk
+            nf = min(self.chunk, self.n_frames - f0)
+            with torch.cuda.stream(self.s_in):
+                if ev_k[s] is not None:
+                    self.s_in.wait_event(ev_k[s])            # kernels of chunk c-2 are done with d_in[s]
+                self.d_in[s][: nf * self.n].copy_(pinned_points[f0 * self.n:(f0 + nf) * self.n], non_blocking=True)
+                ev_in[s] = torch.cuda.Event(); ev_in[s].record(self.s_in)
+            with torch.cuda.stream(self.s_k):
+                self.s_k.wait_event(ev_in[s])
+                if ev_out[s] is not None:
+                    self.s_k.wait_event(ev_out[s])           # D2H of chunk c-2 is done with d_out[s]
+                self.pr.project(self.d_in[s], n_frames=nf, uniform_n=self.n, out=self.d_out[s],
+                                stream=self.s_k.cuda_stream)
+                ev_k[s] = torch.cuda.Event(); ev_k[s].record(self.s_k)
+            with torch.cuda.stream(self.s_out):
+                self.s_out.wait_event(ev_k[s])
+                o = self.d_out[s]
+                if self.h_range is not None:
+                    self.h_range[f0:f0 + nf].copy_(o["range"][:nf], non_blocking=True)
+                if self.h_bev is not None:
+                    self.h_bev[f0:f0 + nf].copy_(o["bev"][:nf], non_blocking=True)
+                self.h_status[f0:f0 + nf].copy_(o["status"][:nf], non_blocking=True)
+                ev_out[s] = torch.cuda.Event(); ev_out[s].record(self.s_out)
+        return self

@@ -1,0 +1,206 @@
+"""Parity of the CUDA path (through the C ABI) against the reference goldens and the oracle.
+
+Bit-exact for cell assignment, winners, counts and the float64 range images; the
+log-normalised density is compared at rtol 1e-6 (BASELINE.json north_star tolerance)."""
+import numpy as np
+import pytest
+
+from conftest import golden, load_pkg
+from oracle import lidar_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+FRONT = ["hdl32_seed0", "hdl32_seed1_shuffled_dropout", "hdl64_seed2", "vls128_seed3_near",
+         "small_seed4", "edges"]
+DENSITY_RTOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import torch
+    assert torch.cuda.is_available()
+    return load_pkg()
+
+
+def _P(pts32):
+    p = np.zeros((len(pts32), 5))
+    p[:, :4] = pts32
+    return p
+
+
+# ---------------------------------------------------------------- drop-in entries vs reference goldens
+@pytest.mark.parametrize("name", FRONT)
+def test_dropin_front_view_vs_reference_golden(pkg, name):
+    g = golden(name)
+    P = _P(g["points"])
+    out = pkg.generate_lidar_2d_front_view(P)
+    tie = lo.front_view(P)["tie_mask"]
+    for k in ("distance", "height", "intensity"):
+        a = out[k + "_float"]
+        assert a.dtype == np.float64 and a.shape == (32, 1801)
+        assert np.array_equal(a[~tie], g[k][~tie]), k
+        assert out[k] is not None
+    img, flt = pkg.lidar_2d_front_view(P, res=(1.33, 0.2), fov=(-30.67, 10.67), type="height")
+    assert np.array_equal(flt[~tie], g["height"][~tie]) and img is flt
+
+
+@pytest.mark.parametrize("name", FRONT + ["bev_edges"])
+def test_dropin_bev_density_vs_reference_golden(pkg, name):
+    g = golden(name)
+    P = _P(g["points"])
+    for key in [k for k in g.files if k.startswith("bev_")]:
+        r = float(key[4:])
+        d = pkg.birds_eye_view_density(P, (r, r), 120)
+        assert d.shape == g[key].shape and d.dtype == np.float64
+        assert np.array_equal(d == 0, g[key] == 0), key           # occupancy is exact
+        np.testing.assert_allclose(d, g[key], rtol=DENSITY_RTOL, atol=0)
+        rgb = pkg.generate_birds_eye_view(P, 0, (r, r), 120)
+        assert rgb.dtype == np.uint8 and rgb.shape == d.shape + (3,)
+
+
+@pytest.mark.parametrize("name", ["raises_high_elevation", "raises_origin", "raises_nan", "raises_low_elevation"])
+def test_dropin_raises_like_reference(pkg, name):
+    g = golden(name)
+    with pytest.raises(IndexError):
+        pkg.generate_lidar_2d_front_view(_P(g["points"]))
+
+
+def test_dropin_asserts_like_reference(pkg):
+    P = _P(golden("small_seed4")["points"])
+    with pytest.raises(AssertionError):
+        pkg.lidar_2d_front_view(P, res=(1.33,), fov=(-30.67, 10.67), type="height")
+    with pytest.raises(AssertionError):
+        pkg.lidar_2d_front_view(P, res=(1.33, 0.2), fov=(1.0, 10.67), type="height")
+    with pytest.raises(AssertionError):
+        pkg.lidar_2d_front_view(P, res=(1.33, 0.2), fov=(-30.67, 10.67), type="depth")
+
+
+# ---------------------------------------------------------------- batched device API vs oracle
+def _run_batch(pkg, sweeps, ragged=True, **kw):
+    import torch
+    allp = np.concatenate(sweeps) if sweeps else np.zeros((0, 4), np.float32)
+    offs = np.zeros(len(sweeps) + 1, np.int64)
+    offs[1:] = np.cumsum([len(s) for s in sweeps])
+    proj_kw = {k: kw.pop(k) for k in list(kw) if k in ("bev_res", "max_range", "key_prefix_bits", "path",
+                                                       "extrinsic", "slice_edges")}
+    pr = pkg.LidarProjector(device=0, **proj_kw)
+    d = torch.from_numpy(allp).cuda() if len(allp) else torch.zeros((1, 4), dtype=torch.float32, device="cuda")
+    if ragged:
+        out = pr.project(d, n_frames=len(sweeps), frame_offsets=torch.from_numpy(offs).cuda(),
+                         max_n=max([len(s) for s in sweeps] + [0]), winner=True, counts=True, **kw)
+    else:
+        out = pr.project(d, n_frames=len(sweeps), winner=True, counts=True, **kw)
+    torch.cuda.synchronize()
+    res = {k: v.cpu().numpy() for k, v in out.items() if hasattr(v, "cpu")}
+    res["_path"] = pr.last_path
+    pr.close()
+    return res
+
+
+def _check_frame(res, f, pts32, bev_res=(0.2, 0.2), layout="hwc", strict_ok=True):
+    P = _P(pts32)
+    o = lo.front_view(P, strict=False)
+    assert np.array_equal(res["winner"][f], o["winner"].astype(np.int32))
+    rng = res["range"][f]
+    if layout == "hwc":
+        rng = np.moveaxis(rng, -1, 0)
+    for c, k in enumerate(("distance", "height", "intensity")):
+        assert np.array_equal(rng[c], o[k].astype(rng.dtype)), k
+    assert res["status"][f] == o["err"] and res["dropped"][f] == o["dropped"]
+    cnt = lo.bev_counts(P, bev_res, 120)
+    assert np.array_equal(res["counts"][f], cnt.astype(np.int32))
+    dens = lo.bev_density(P, bev_res, 120)
+    np.testing.assert_allclose(res["bev"][f], dens.astype(res["bev"].dtype), rtol=DENSITY_RTOL, atol=0)
+
+
+def test_batch_ragged_f32_hwc(pkg, synth):
+    sweeps = [synth.make_sweep("hdl32", seed=20), synth.make_sweep("hdl32", seed=21, dropout=0.3, shuffle=True),
+              np.zeros((0, 4), np.float32), synth.make_sweep("hdl64", seed=22, n_az=200),
+              synth.make_sweep("hdl32", seed=23, n_az=1)]
+    res = _run_batch(pkg, sweeps)
+    for f, s in enumerate(sweeps):
+        _check_frame(res, f, s)
+    # an empty frame is pure background
+    assert (res["winner"][2] == -1).all() and (res["bev"][2] == 0).all()
+    assert (res["range"][2][..., 1] == -2.0).all() and (res["range"][2][..., 0] == 0).all()
+
+
+def test_batch_uniform_f64_chw(pkg, synth):
+    sweeps = [synth.make_sweep("hdl32", seed=30 + i, n_az=300) for i in range(40)]   # > one scratch chunk
+    res = _run_batch(pkg, sweeps, ragged=False, range_dtype="f64", range_layout="chw", bev_dtype="f64")
+    for f in (0, 1, 17, 39):
+        _check_frame(res, f, sweeps[f], layout="chw")
+
+
+def test_batch_other_bev_resolutions(pkg, synth):
+    sweeps = [synth.make_sweep("vls128", seed=40, n_az=400, near_heavy=True), synth.make_sweep("hdl32", seed=41)]
+    for res_m in ((2, 2), (0.5, 0.25), (0.1, 0.1)):
+        res = _run_batch(pkg, sweeps, bev_res=res_m)
+        for f, s in enumerate(sweeps):
+            _check_frame(res, f, s, bev_res=res_m)
+
+
+def test_invalid_points_are_dropped_and_flagged(pkg, synth):
+    base = synth.make_sweep("hdl32", seed=50, n_az=64)
+    bad = np.array([[0, 0, 0, 1], [np.nan, 1, 1, 1], [1, 0, 5, 1], [1, 0, -30, 2], [np.inf, 1, 1, 1]], np.float32)
+    sweeps = [np.vstack([base, bad]), base]
+    res = _run_batch(pkg, sweeps)
+    for f, s in enumerate(sweeps):
+        _check_frame(res, f, s)
+    assert res["status"][0] != 0 and res["status"][1] == 0 and res["dropped"][0] >= 3
+
+
+@pytest.mark.parametrize("prefix_bits", [8, 12, 16, 24])
+def test_forced_key_collisions_settle_exactly(pkg, synth, prefix_bits):
+    """With only a few range bits in the packed key nearly every multi-point cell takes the
+    exact-compare CAS path; the winners must still equal the oracle's."""
+    sweeps = [synth.make_sweep("hdl32", seed=60), synth.make_sweep("vls128", seed=61, n_az=600, shuffle=True)]
+    res = _run_batch(pkg, sweeps, key_prefix_bits=prefix_bits)
+    for f, s in enumerate(sweeps):
+        _check_frame(res, f, s)
+
+
+def test_near_equal_and_duplicate_ranges(pkg):
+    rng = np.random.default_rng(3)
+    base = np.array([8.0, 1.0, -0.25], np.float32)
+    pts = []
+    for k in range(200):                      # same cell, ranges differing in the last float32 bits
+        p = base.copy()
+        p[rng.integers(0, 3)] = np.nextafter(p[rng.integers(0, 3)], np.float32(100), dtype=np.float32)
+        for _ in range(int(rng.integers(0, 4))):
+            j = rng.integers(0, 3)
+            p[j] = np.nextafter(p[j], np.float32(100 if rng.random() < 0.5 else -100), dtype=np.float32)
+        pts.append([p[0], p[1], p[2], float(k)])
+    pts += pts[:50]                           # exact duplicates: tie -> lowest index
+    pts = np.array(pts, np.float32)
+    res = _run_batch(pkg, [pts, pts[::-1].copy()])
+    _check_frame(res, 0, pts)
+    _check_frame(res, 1, pts[::-1].copy())
+
+
+def test_float64_inputs_not_float32_representable(pkg):
+    """The drop-in takes the reference's float64 (N,5) arrays as they are."""
+    rng = np.random.default_rng(5)
+    n = 5000
+    az = rng.uniform(-np.pi, np.pi, n); el = np.deg2rad(rng.uniform(-30, 10, n)); r = rng.uniform(1, 90, n)
+    P = np.stack([r * np.cos(el) * np.cos(az), r * np.cos(el) * np.sin(az), r * np.sin(el),
+                  rng.uniform(0, 255, n), rng.integers(0, 32, n).astype(float)], axis=1)
+    o = lo.front_view(P)
+    out = pkg.generate_lidar_2d_front_view(P)
+    for k in ("distance", "height", "intensity"):
+        assert np.array_equal(out[k + "_float"][~o["tie_mask"]], o[k][~o["tie_mask"]]), k
+    d = pkg.birds_eye_view_density(P, (0.2, 0.2), 120)
+    np.testing.assert_allclose(d, lo.bev_density(P, (0.2, 0.2), 120), rtol=DENSITY_RTOL, atol=0)
+
+
+def test_order_invariance_and_conservation(pkg, synth):
+    """Size-independent properties at the bench's sweep size: shuffling the points changes
+    nothing but the winner indices; every in-range point is counted exactly once."""
+    s = synth.make_sweep("hdl32", seed=70)
+    perm = np.random.default_rng(0).permutation(len(s))
+    res = _run_batch(pkg, [s, s[perm]])
+    assert np.array_equal(res["range"][0], res["range"][1])
+    assert np.array_equal(res["counts"][0], res["counts"][1])
+    assert np.array_equal(perm[res["winner"][1][res["winner"][1] >= 0]], res["winner"][0][res["winner"][0] >= 0])
+    inside = (np.abs(s[:, 0].astype(np.float64)) < 119.7) & (np.abs(s[:, 1].astype(np.float64)) < 119.7)
+    assert res["counts"][0].sum() >= inside.sum() and res["counts"][0].sum() <= len(s)
