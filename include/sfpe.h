@@ -21,7 +21,7 @@
  * Conventions: every function returns 0 (SFPE_OK) or a negative sfpe_status; nothing throws
  * across the ABI.  All buffers are owned by the caller; the library owns only scratch
  * inside the ctx.  "device" pointers are CUDA device pointers of the ctx's device.
- * `stream` is a cudaStream_t passed as void* (NULL = the ctx's own stream).  One ctx per
+ * `stream` is a cudaStream_t passed as void* (NULL = the CUDA default stream, as in CUDA itself).  One ctx per
  * device per thread; a ctx is not re-entrant.  There is NO CPU fallback: without a CUDA
  * device sfpe_create fails with SFPE_ERR_CUDA.
  */

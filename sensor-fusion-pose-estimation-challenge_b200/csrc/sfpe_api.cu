@@ -26,6 +26,7 @@ struct sfpe_ctx {
   void* st_range; void* st_bev; int* st_winner; int* st_status;  // status[0], dropped[1]
   unsigned long long* d_mm;  // colormap autoscale {min,max}
   void* st_img; size_t st_img_cap; void* st_rgb; size_t st_rgb_cap;
+  void* fused_buf; size_t fused_cap;  // entries + deferred queue of the fused path
 };
 
 #define CK(ctx, call)                                                                   \
@@ -109,6 +110,12 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
     if (i && !(p->slice_edges[i] > p->slice_edges[i - 1])) return SFPE_ERR_INVALID_ARG;
   }
   g->idx_bits = 20;
+  g->bev_inv_delta_x = g->enable_bev ? 1.0 / g->bev_delta_x : 0.0;
+  g->bev_inv_delta_y = g->enable_bev ? 1.0 / g->bev_delta_y : 0.0;
+  g->inv_res_h_f = (float)(1.0 / g->res_rad_h);
+  g->inv_res_v_f = (float)(1.0 / g->res_rad_v);
+  g->neg_x_min_f = (float)(-g->x_min);
+  g->neg_y_min_f = (float)(-g->y_min);
   return SFPE_OK;
 }
 
@@ -196,7 +203,7 @@ extern "C" void sfpe_destroy(sfpe_ctx* c) {
   cudaFree(c->scratch.keys); cudaFree(c->scratch.counts); cudaFree(c->scratch.top);
   cudaFree(c->scratch.slice_max); cudaFree(c->d_lut);
   cudaFree(c->st_points); cudaFree(c->st_range); cudaFree(c->st_bev); cudaFree(c->st_winner);
-  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb);
+  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb); cudaFree(c->fused_buf);
   if (c->stream) cudaStreamDestroy(c->stream);
   free(c);
 }
@@ -204,6 +211,15 @@ extern "C" void sfpe_destroy(sfpe_ctx* c) {
 extern "C" const char* sfpe_last_error(const sfpe_ctx* c) { return c ? c->err : "null ctx"; }
 extern "C" int64_t sfpe_launch_count(const sfpe_ctx* c) { return c ? c->launches : 0; }
 extern "C" const char* sfpe_last_path(const sfpe_ctx* c) { return c ? c->last_path : "none"; }
+
+static int grow(sfpe_ctx* c, void** p, size_t* cap, size_t need) {
+  if (*cap >= need) return SFPE_OK;
+  if (*p) CK(c, cudaFree(*p));
+  *p = nullptr; *cap = 0;
+  CK(c, cudaMalloc(p, need));
+  *cap = need;
+  return SFPE_OK;
+}
 
 static int ceil_log2(long long v) {
   int b = 0;
@@ -227,7 +243,7 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     return SFPE_ERR_INVALID_ARG;
   if (n_frames == 0) return SFPE_OK;
   CK(c, cudaSetDevice(c->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the CUDA default stream
 
   DevGrid g = c->grid;
   const int need = ceil_log2(max_n > 1 ? max_n : 1);
@@ -256,9 +272,18 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
   FrameSet fs;
   fs.offsets = (const long long*)d_offsets; fs.uniform_n = uniform_n;
   const int want = c->params.path;
-  if (want != 1 && fused_supported(g, src, out, c->device)) {
+  if (want != 1 && fused_supported(g, src, out, max_n)) {
+    FusedScratch fx;
+    fx.grid = fused_grid(c->device, n_frames);
+    fx.per_cta = (max_n + 255) & ~255ll;
+    if (fx.per_cta < 256) fx.per_cta = 256;
+    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * 2;
+    const int grc = grow(c, &c->fused_buf, &c->fused_cap, need);
+    if (grc) return grc;
+    fx.entries = (unsigned*)c->fused_buf;
+    fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta;
     fs.frame0 = 0; fs.n_frames = n_frames;
-    CK(c, launch_fused(g, src, fs, max_n, c->scratch, out, c->device, st, &c->launches));
+    CK(c, launch_fused(g, src, fs, c->scratch, out, fx, st, &c->launches));
     c->last_path = "fused";
     return SFPE_OK;
   }
@@ -272,14 +297,6 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
   return SFPE_OK;
 }
 
-static int grow(sfpe_ctx* c, void** p, size_t* cap, size_t need) {
-  if (*cap >= need) return SFPE_OK;
-  if (*p) CK(c, cudaFree(*p));
-  *p = nullptr; *cap = 0;
-  CK(c, cudaMalloc(p, need));
-  *cap = need;
-  return SFPE_OK;
-}
 
 extern "C" int sfpe_project_sweep_host(sfpe_ctx* c, const void* h_points, const sfpe_points* layout, int64_t n,
                                        void* h_range, int32_t range_dtype, int32_t range_layout, int32_t* h_winner,
@@ -333,7 +350,7 @@ extern "C" int sfpe_decode_pointcloud2(sfpe_ctx* c, const void* d_blob, int64_t 
       ((uintptr_t)d_xyzi % 16))
     return SFPE_ERR_INVALID_ARG;
   CK(c, cudaSetDevice(c->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the CUDA default stream
   CK(c, launch_decode_pc2(d_blob, n, point_step, off_x, off_y, off_z, off_i, dtype, d_xyzi, st, &c->launches));
   return SFPE_OK;
 }
@@ -344,7 +361,7 @@ extern "C" int sfpe_colormap(sfpe_ctx* c, const void* d_img, int32_t dtype, int6
   if ((dtype != SFPE_F32 && dtype != SFPE_F64) || (cmap != SFPE_CMAP_GRAY && cmap != SFPE_CMAP_JET))
     return SFPE_ERR_INVALID_ARG;
   CK(c, cudaSetDevice(c->device));
-  cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+  cudaStream_t st = (cudaStream_t)stream;  // NULL = the CUDA default stream
   CK(c, launch_colormap(d_img, dtype, n, cmap, autoscale != 0, vmin, vmax, c->d_mm, d_rgb, st, &c->launches));
   return SFPE_OK;
 }

@@ -31,6 +31,10 @@ struct DevGrid {
   int enable_range, enable_bev;
   double M[12];
   double slice_edges[9];
+  // fast path constants (fused kernel)
+  double bev_inv_delta_x, bev_inv_delta_y;   // 1/delta (candidate bin only; edges decide)
+  float inv_res_h_f, inv_res_v_f;            // 1/RES_RAD[1], 1/RES_RAD[0]
+  float neg_x_min_f, neg_y_min_f;            // -X_MIN, -Y_MIN
 };
 
 struct PointSrc {
@@ -152,6 +156,42 @@ __device__ __forceinline__ int bev_bin_f64(double v, double start, double delta,
   while (i > 0 && v < bev_edge(start, delta, i)) --i;
   while (i < n_edges - 2 && v >= bev_edge(start, delta, i + 1)) ++i;
   return i;
+}
+
+// ---- fast path helpers (fused kernel) -------------------------------------------------
+// Guard bands of the fp32 cell computation: a point whose fp32 cell coordinate lies within
+// EPS of a (non-zero) integer is re-done in fp64.  Bounds: atan2f/asinf <= 2 ulp (CUDA math
+// API), one fp32 division and one fma -> |xi32 - xi64| < 2.6e-4 cells, |yi32 - yi64| < 3e-5
+// cells for |z/rho| < 0.95 ("fp32 fast path"); sfpe_selftest_fastpath measures it.
+constexpr float EPS_COL = 1.0e-3f;
+constexpr float EPS_ROW = 2.5e-4f;
+constexpr float MAX_SIN_EL = 0.95f;
+
+// fp32 range-scan cell.  Returns true when (row, col) is PROVEN equal to the fp64 result and
+// inside the image; false -> the caller must use range_cell_f64.
+__device__ __forceinline__ bool range_cell_fast(const DevGrid& g, float x, float y, float z, float rho32, int& row,
+                                                int& col) {
+  const float xi = fmaf(atan2f(-y, x), g.inv_res_h_f, g.neg_x_min_f);
+  const float q = z / rho32;
+  const float yi = fmaf(asinf(q), g.inv_res_v_f, g.neg_y_min_f);
+  const float cx = rintf(xi), cy = rintf(yi);
+  // trunc-toward-zero semantics: the cell boundaries are the NON-ZERO integers
+  const bool near_x = fabsf(xi - cx) <= EPS_COL && cx != 0.0f;
+  const bool near_y = fabsf(yi - cy) <= EPS_ROW && cy != 0.0f;
+  col = (int)xi;
+  row = (int)yi;
+  // written so that NaN anywhere gives false
+  return !near_x && !near_y && fabsf(q) < MAX_SIN_EL && xi > -0.5f && yi > -0.5f && col < g.W && row < g.H;
+}
+
+// BEV bin with one fp64 multiply for the candidate and the exact np.arange edges for the
+// decision; falls back to bev_bin_f64 near the ends or when the candidate is off by one.
+__device__ __forceinline__ int bev_bin_fast(double v, double start, double delta, double inv_delta, int n_edges) {
+  const double t = (v - start) * inv_delta;
+  if (!(t >= 0.0) || !(t < (double)(n_edges - 2))) return bev_bin_f64(v, start, delta, n_edges);
+  const int i = (int)t;
+  if (v >= bev_edge(start, delta, i) && v < bev_edge(start, delta, i + 1)) return i;
+  return bev_bin_f64(v, start, delta, n_edges);
 }
 
 }  // namespace sfpe

@@ -55,9 +55,16 @@ cudaError_t launch_decode_pc2(const void* blob, long long n, int step, int ox, i
 cudaError_t launch_colormap(const void* img, int dtype, long long n, int cmap, int autoscale, double vmin, double vmax,
                             unsigned long long* mm, unsigned char* rgb, cudaStream_t st, long long* launches);
 
-// fused cluster path -- sfpe_fused.cu
-bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, int device);
-cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, long long max_n,
-                         const Scratch& s, const DevOut& out, int device, cudaStream_t st, long long* launches);
+// fused one-sweep-per-SM path -- sfpe_fused.cu
+struct FusedScratch {
+  unsigned* entries;   // [grid][per_cta]
+  unsigned* queue;     // [grid][per_cta]
+  long long per_cta;   // >= max points of a frame
+  int grid;            // CTAs (<= SMs)
+};
+bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n);
+int fused_grid(int device, int n_frames);
+cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
+                         const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches);
 
 }  // namespace sfpe

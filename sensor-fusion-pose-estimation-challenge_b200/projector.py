@@ -173,7 +173,7 @@ class LidarProjector:
         if stream is None:
             stream = torch.cuda.current_stream(self.device).cuda_stream
         rc = self.lib.sfpe_project_batch(self._ctx, C.byref(desc), offs_ptr, un, int(max_n), int(n_frames),
-                                         C.byref(o), C.c_void_p(stream) if stream else None)
+                                         C.byref(o), C.c_void_p(int(stream)))
         _lib.check(rc, self._ctx)
         return out
 
