@@ -217,6 +217,19 @@ def run_ours(a):
     if not a.no_e2e:
         e2e = run_e2e(a, pkg, pr, pin_in, dev, world)
 
+    # ---- optional: per-phase SM cycles of the fused kernel (separate untimed steps)
+    phases = None
+    if a.phases and rank == 0:
+        pr.phase_profile(True)
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        cyc = pr.phase_cycles()
+        pr.phase_profile(False)
+        tot = float(sum(cyc.values())) or 1.0
+        phases = {k: round(v / tot, 4) for k, v in cyc.items() if v}
+        phases["sm_cycles_per_sweep"] = tot / (2 * a.sweeps)
+
     status_bad = int((out["status"] != 0).sum().item())
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -238,6 +251,8 @@ def run_ours(a):
                          else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
             "clocks": clocks,
         }
+        if phases is not None:
+            line["phase_share"] = phases
         if e2e is not None:
             line["e2e"] = e2e
         if not a.no_cpu and world == 1:
@@ -291,6 +306,7 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=32)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--phases", action="store_true", help="also report the fused kernel's per-phase cycle shares")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
     sens = {"hdl32": 65536, "hdl64": 120000, "vls128": 249984}

@@ -178,6 +178,14 @@ SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);
 /* Name of the code path the last sfpe_project_batch took ("generic", "fused"). */
 SFPE_API const char* sfpe_last_path(const sfpe_ctx* ctx);
 
+/* Profiling hook (no reference counterpart; the reference's analogue is the cProfile toggle at
+ * team_sf_rosnode/scripts/lidar_predict.py:21-23).  enable != 0: the fused kernel accumulates SM
+ * cycles per phase (and the counters are reset); 0: off.  sfpe_phase_cycles synchronises the
+ * device and returns the sums over all CTAs: out8[0..7] = key init, point pass, deferred fp64
+ * pass, range-scan resolve, BEV tile compose, BEV exact redo, BEV tile write, unused. */
+SFPE_API int sfpe_phase_profile(sfpe_ctx* ctx, int32_t enable);
+SFPE_API int sfpe_phase_cycles(sfpe_ctx* ctx, int64_t* out8);
+
 #ifdef __cplusplus
 }
 #endif

@@ -27,6 +27,7 @@ struct sfpe_ctx {
   unsigned long long* d_mm;  // colormap autoscale {min,max}
   void* st_img; size_t st_img_cap; void* st_rgb; size_t st_rgb_cap;
   void* fused_buf; size_t fused_cap;  // entries + deferred queue of the fused path
+  long long* d_prof; int prof_grid;   // phase profile of the fused kernel (sfpe_phase_profile)
 };
 
 #define CK(ctx, call)                                                                   \
@@ -203,7 +204,7 @@ extern "C" void sfpe_destroy(sfpe_ctx* c) {
   cudaFree(c->scratch.keys); cudaFree(c->scratch.counts); cudaFree(c->scratch.top);
   cudaFree(c->scratch.slice_max); cudaFree(c->d_lut);
   cudaFree(c->st_points); cudaFree(c->st_range); cudaFree(c->st_bev); cudaFree(c->st_winner);
-  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb); cudaFree(c->fused_buf);
+  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb); cudaFree(c->fused_buf); cudaFree(c->d_prof);
   if (c->stream) cudaStreamDestroy(c->stream);
   free(c);
 }
@@ -283,6 +284,7 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.entries = (unsigned*)c->fused_buf;
     fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta;
     fs.frame0 = 0; fs.n_frames = n_frames;
+    fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;
     CK(c, launch_fused(g, src, fs, c->scratch, out, fx, st, &c->launches));
     c->last_path = "fused";
     return SFPE_OK;
@@ -382,5 +384,40 @@ extern "C" int sfpe_colormap_host(sfpe_ctx* c, const void* h_img, int32_t dtype,
   if (rc) return rc;
   CK(c, cudaMemcpyAsync(h_rgb, c->st_rgb, (size_t)n * 3, cudaMemcpyDeviceToHost, c->stream));
   CK(c, cudaStreamSynchronize(c->stream));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_phase_profile(sfpe_ctx* c, int32_t enable) {
+  if (!c) return SFPE_ERR_INVALID_ARG;
+  CK(c, cudaSetDevice(c->device));
+  if (!enable) {
+    if (c->d_prof) CK(c, cudaFree(c->d_prof));
+    c->d_prof = nullptr;
+    return SFPE_OK;
+  }
+  if (!c->d_prof) {
+    int sms = 0;
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    c->prof_grid = sms;
+    CK(c, cudaMalloc((void**)&c->d_prof, (size_t)sms * 8 * sizeof(long long)));
+  }
+  CK(c, cudaMemset(c->d_prof, 0, (size_t)c->prof_grid * 8 * sizeof(long long)));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_phase_cycles(sfpe_ctx* c, int64_t* out8) {
+  if (!c || !out8) return SFPE_ERR_INVALID_ARG;
+  for (int i = 0; i < 8; ++i) out8[i] = 0;
+  if (!c->d_prof) return SFPE_OK;
+  CK(c, cudaSetDevice(c->device));
+  CK(c, cudaDeviceSynchronize());
+  long long* h = (long long*)malloc((size_t)c->prof_grid * 8 * sizeof(long long));
+  if (!h) return SFPE_ERR_NOMEM;
+  cudaError_t e = cudaMemcpy(h, c->d_prof, (size_t)c->prof_grid * 8 * sizeof(long long), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess)
+    for (int b = 0; b < c->prof_grid; ++b)
+      for (int i = 0; i < 8; ++i) out8[i] += h[b * 8 + i];
+  free(h);
+  CK(c, e);
   return SFPE_OK;
 }

@@ -9,11 +9,17 @@
 //           prefixes are settled exactly on the fp64 rho (CAS loop); guard-band / out-of-image
 //           points go to a deferred queue that is re-done in fp64 (S1b)
 //         - exact BEV bin (np.arange edges in fp64) -> flat output cell written to an entry list
-//   S1c range scan resolved from shared memory: winner point gathered, 3 channels written once
+//           (L2 evict_last: it is re-read once per BEV tile)
+//   S1c range scan resolved from shared memory, column-major over the image so that the winner
+//       gathers of a warp hit neighbouring points; 3 channels written once with 16-byte stores
 //   S2  BEV composed in shared memory as saturating u8 counts, one flat tile of the output at a
-//       time: filter the entry list, then write the tile ONCE with aligned 16-byte streaming
-//       stores (count -> 255*min(ln(N+1)/ln64,1) through a LUT), re-zeroing the tile in place
-// Every output byte is written exactly once from registers; nothing is read back from HBM.
+//       time: filter the entry list, then write the 32-byte sectors that hold a non-empty cell
+//   ZF  the BEV image is >95 % zeros and the per-SM store path (~30 B/clk) is the longest single
+//       resource of a sweep, so the zero fill of the frame is not a phase: every thread pumps a
+//       few 16-byte zero stores per iteration of S1 / S1c / S2-compose, and only catches up (if
+//       needed) before the non-empty sectors of a tile are written over the zeros.
+// HBM traffic: points read once (+ the winner gather), range written once, BEV written once plus
+// the non-empty sectors a second time.
 #include "sfpe_internal.h"
 
 namespace sfpe {
@@ -24,7 +30,23 @@ constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
 constexpr int SMEM_MISC_WORDS = 128;                 // LUT (65 floats) + counters
+constexpr int ENTRY_BATCH = 16;                      // entry loads in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
+
+// ---- L2 residency hints: the entry list is written once and read once per BEV tile
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+  unsigned long long p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void st_u32_hint(unsigned* ptr, unsigned v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(ptr), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ unsigned ld_u32_hint(const unsigned* ptr, unsigned long long pol) {
+  unsigned v;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(ptr), "l"(pol));
+  return v;
+}
 
 // monotone non-decreasing map rho (fp64, >= 0 or +inf) -> 14 bits: 1/64 m steps, saturating
 __device__ __forceinline__ unsigned quant_rho(double rho) {
@@ -91,6 +113,30 @@ __device__ __forceinline__ void tile_count_exact(unsigned* tile, unsigned r) {
   }
 }
 
+// Zero-fill pump: up to `cnt` 16-byte zero stores of this thread's share of the frame's BEV
+// (word `cur`, then cur + FUSED_THREADS, ...).  Streaming (evict-first) stores.
+__device__ __forceinline__ void zf_pump(float4* __restrict__ zbase, int& cur, const int end, const int cnt) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int u = 0; u < cnt; ++u) {
+    if (cur < end) __stcs(zbase + cur, z);
+    cur += FUSED_THREADS;
+  }
+}
+__device__ __forceinline__ void zf_until(float4* __restrict__ zbase, int& cur, const int end, const int upto) {
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int lim = upto < end ? upto : end;
+#pragma unroll 4
+  for (; cur < lim; cur += FUSED_THREADS) __stcs(zbase + cur, z);
+}
+
+__device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
+  float4 v;
+  v.x = lut[min(word & 0xFFu, 64u)]; v.y = lut[min((word >> 8) & 0xFFu, 64u)];
+  v.z = lut[min((word >> 16) & 0xFFu, 64u)]; v.w = lut[min(word >> 24, 64u)];
+  return v;
+}
+
 struct FusedArgs {
   const float4* pts;
   FrameSet fs;
@@ -99,10 +145,22 @@ struct FusedArgs {
   long long per_cta;
   const double* lut64;
   float* range; int range_layout; int* winner;
+  int range_vec4;      // H*W % 4 == 0 and 16-byte aligned range / winner buffers: vector resolve
   float* bev;
   int* status; int* dropped;
   int tile_cells;      // BEV cells per shared-memory tile (multiple of 16)
+  long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
 };
+
+// phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph`
+#define PROF_STAMP(ph)                                          \
+  do {                                                          \
+    if (a.prof && tid == 0) {                                   \
+      const long long now_ = clock64();                         \
+      a.prof[(size_t)blockIdx.x * 8 + (ph)] += now_ - t_prev;   \
+      t_prev = now_;                                            \
+    }                                                           \
+  } while (0)
 
 __global__ void __launch_bounds__(FUSED_THREADS, 1)
 k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedArgs a, const int main_words) {
@@ -117,52 +175,82 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   unsigned* const my_entries = a.entries + (size_t)blockIdx.x * a.per_cta;
   unsigned* const my_queue = a.queue + (size_t)blockIdx.x * a.per_cta;
   const float height_bg = (float)g.height_bg;
+  const unsigned cells_m1 = (unsigned)(cells - 1);
+  const unsigned long long keep = l2_policy_evict_last();
+  const bool do_bev = g.enable_bev && a.bev;
   if (tid < 65) lut[tid] = (float)a.lut64[tid];
+  long long t_prev = clock64();
 
   for (int f = a.fs.frame0 + blockIdx.x; f < a.fs.frame0 + a.fs.n_frames; f += gridDim.x) {
     long long base, n;
     frame_span(a.fs, f, base, n);
     const float4* __restrict__ fp = a.pts + base;
 
+    // ---- ZF set-up: this frame's BEV is cells [E0, E1) of a.bev; full 16-byte words
+    // [W0, W1) are zero-filled by the pump, the (<= 3 + 3) head / tail cells right here.
+    const long long E0 = (long long)f * cells, E1 = E0 + cells;
+    float4* zbase = nullptr;
+    int zcur = tid, zend = 0;
+    if (do_bev) {
+      const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
+      zbase = reinterpret_cast<float4*>(a.bev) + W0;
+      zend = W1 > W0 ? (int)(W1 - W0) : 0;
+      if (tid < 8) {   // head cells [E0, 4*W0) and tail cells [4*W1, E1), clipped to the frame
+        const long long c = tid < 4 ? E0 + tid : 4 * W1 + (tid - 4);
+        const bool mine = tid < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
+        if (mine) a.bev[c] = 0.f;
+      }
+    }
+    const int zper = (zend + FUSED_THREADS - 1) / FUSED_THREADS;   // zero stores per thread per frame
+
     // ---- S0
     if (g.enable_range)
       for (int i = tid; i < hw; i += FUSED_THREADS) keys[i] = KEY32_EMPTY;
     if (tid < 4) misc[tid] = 0u;
     __syncthreads();
+    PROF_STAMP(0);
 
-    // ---- S1: one pass over the points
-    for (long long i0 = 0; i0 < n; i0 += 4 * FUSED_THREADS) {
-      float4 v[4];
+    // ---- S1: one pass over the points (+ ~5/8 of the zero fill)
+    {
+      const long long iters = (n + 4 * FUSED_THREADS - 1) / (4 * FUSED_THREADS);
+      const int k1 = iters ? (int)((((long long)zper * 5 >> 3) + iters - 1) / iters) : 0;
+      for (long long i0 = 0; i0 < n; i0 += 4 * FUSED_THREADS) {
+        float4 v[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const long long i = i0 + u * FUSED_THREADS + tid;
-        if (i < n) v[u] = __ldg(fp + i);
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const long long i = i0 + u * FUSED_THREADS + tid;
-        if (i >= n) continue;
-        if (g.enable_bev) {
-          const int bx = bev_bin_fast((double)v[u].x, g.bev_start, g.bev_delta_x, g.bev_inv_delta_x, g.nex);
-          const int by = bev_bin_fast((double)v[u].y, g.bev_start, g.bev_delta_y, g.bev_inv_delta_y, g.ney);
-          // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
-          my_entries[i] = (bx >= 0 && by >= 0) ? (unsigned)(cells - 1 - ((long long)bx * g.nby + by)) : 0xFFFFFFFFu;
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * FUSED_THREADS + tid;
+          if (i < n) v[u] = __ldg(fp + i);
         }
-        if (g.enable_range) {
-          const double rho = rho_of_f4(v[u]);
-          int row, col;
-          if (range_cell_fast(g, v[u].x, v[u].y, v[u].z, (float)rho, row, col)) {
-            key_min32(fp, keys, row * g.W + col, rho, (unsigned)i);
-          } else {
-            my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
+        zf_pump(zbase, zcur, zend, k1);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const long long i = i0 + u * FUSED_THREADS + tid;
+          if (i >= n) continue;
+          if (g.enable_bev) {
+            const int bx = bev_bin_fast((double)v[u].x, g.bev_start, g.bev_delta_x, g.bev_inv_delta_x, g.nex);
+            const int by = bev_bin_fast((double)v[u].y, g.bev_start, g.bev_delta_y, g.bev_inv_delta_y, g.ney);
+            // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
+            st_u32_hint(my_entries + i,
+                        (bx >= 0 && by >= 0) ? cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) : 0xFFFFFFFFu,
+                        keep);
+          }
+          if (g.enable_range) {
+            const double rho = rho_of_f4(v[u]);
+            int row, col;
+            if (range_cell_fast(g, v[u].x, v[u].y, v[u].z, (float)rho, row, col)) {
+              key_min32(fp, keys, row * g.W + col, rho, (unsigned)i);
+            } else {
+              my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
+            }
           }
         }
       }
     }
     __syncthreads();
+    PROF_STAMP(1);
 
-    // ---- S1b: deferred points, full fp64 (guard band, image border, wrap, NaN, errors)
     if (g.enable_range) {
+      // ---- S1b: deferred points, full fp64 (guard band, image border, wrap, NaN, errors)
       const unsigned qn = misc[0];
       for (unsigned j = tid; j < qn; j += FUSED_THREADS) {
         const unsigned i = my_queue[j];
@@ -179,93 +267,173 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         }
       }
       __syncthreads();
+      PROF_STAMP(2);
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
         if (a.dropped) a.dropped[f] = (int)misc[2];
       }
 
       // ---- S1c: resolve the range scan; output row r shows pre-flip row H-1-r   (:74)
-      for (int c = tid; c < hw; c += FUSED_THREADS) {
-        const int orow = c / g.W, col = c - orow * g.W;
-        const unsigned key = keys[(g.H - 1 - orow) * g.W + col];
-        float d = 0.f, h = height_bg, it = 0.f;
-        int win = -1;
-        if (key != KEY32_EMPTY) {
-          win = (int)(key & IDX_MASK32);
-          const float4 v = __ldg(fp + win);
-          const double x = v.x, y = v.y;
-          d = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
-          h = v.z; it = v.w;
-        }
-        if (a.range) {
-          if (a.range_layout == 0) {
-            float* o = a.range + (size_t)f * 3 * hw + c;
-            __stcs(o, d); __stcs(o + hw, h); __stcs(o + 2 * hw, it);
-          } else {
-            float* o = a.range + ((size_t)f * hw + c) * 3;
-            __stcs(o, d); __stcs(o + 1, h); __stcs(o + 2, it);
+      if (a.range_vec4) {
+        // Task (k, r) = k-th aligned group of 4 flat output cells whose first cell lies in output
+        // row r; tasks run k-major / r-minor, so a warp (H = 32: one lane per row) gathers the
+        // winners of ~4 neighbouring columns -- neighbouring points of a firing-order sweep.
+        const int kmax = ((g.W + 3) >> 2) + 1;
+        const int ntask = kmax * g.H;
+        const int k2 = (int)(((long long)(zper >> 3) * FUSED_THREADS + ntask - 1) / ntask);
+        for (int t = tid; t < ntask; t += FUSED_THREADS) {
+          const int k = t / g.H, r = t - k * g.H;
+          const int gid = ((r * g.W + 3) >> 2) + k;
+          zf_pump(zbase, zcur, zend, k2);
+          if (gid >= (((r + 1) * g.W + 3) >> 2)) continue;
+          const int c = gid << 2;
+          int orow = r, col = c - r * g.W;
+          unsigned key[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            key[j] = keys[(g.H - 1 - orow) * g.W + col];
+            if (++col == g.W) { col = 0; ++orow; }
           }
+          float4 v[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (key[j] != KEY32_EMPTY) v[j] = __ldg(fp + (key[j] & IDX_MASK32));
+          float d[4], h[4], it[4];
+          int win[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
+            if (key[j] != KEY32_EMPTY) {
+              win[j] = (int)(key[j] & IDX_MASK32);
+              const double x = v[j].x, y = v[j].y;
+              d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
+              h[j] = v[j].z; it[j] = v[j].w;
+            }
+          }
+          if (a.range) {
+            if (a.range_layout == 0) {
+              float* o = a.range + (size_t)f * 3 * hw + c;
+              __stcs(reinterpret_cast<float4*>(o), make_float4(d[0], d[1], d[2], d[3]));
+              __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
+              __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
+            } else {
+              float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
+              __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
+              __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
+              __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
+            }
+          }
+          if (a.winner)
+            __stcs(reinterpret_cast<int4*>(a.winner + (size_t)f * hw + c), make_int4(win[0], win[1], win[2], win[3]));
         }
-        if (a.winner) __stcs(a.winner + (size_t)f * hw + c, win);
+      } else {
+        for (int c = tid; c < hw; c += FUSED_THREADS) {
+          const int orow = c / g.W, col = c - orow * g.W;
+          const unsigned key = keys[(g.H - 1 - orow) * g.W + col];
+          float d = 0.f, h = height_bg, it = 0.f;
+          int win = -1;
+          if (key != KEY32_EMPTY) {
+            win = (int)(key & IDX_MASK32);
+            const float4 v = __ldg(fp + win);
+            const double x = v.x, y = v.y;
+            d = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
+            h = v.z; it = v.w;
+          }
+          if (a.range) {
+            if (a.range_layout == 0) {
+              float* o = a.range + (size_t)f * 3 * hw + c;
+              __stcs(o, d); __stcs(o + hw, h); __stcs(o + 2 * hw, it);
+            } else {
+              float* o = a.range + ((size_t)f * hw + c) * 3;
+              __stcs(o, d); __stcs(o + 1, h); __stcs(o + 2, it);
+            }
+          }
+          if (a.winner) __stcs(a.winner + (size_t)f * hw + c, win);
+        }
       }
       __syncthreads();
+      PROF_STAMP(3);
     } else if (tid == 0) {
       if (a.status) a.status[f] = 0;
       if (a.dropped) a.dropped[f] = 0;
     }
 
-    // ---- S2: BEV, one flat tile of the output at a time
-    if (g.enable_bev && a.bev) {
-      const long long E0 = (long long)f * cells, E1 = E0 + cells;
+    // ---- S2: BEV, one flat tile of the output at a time.  Tiles start on a 32-byte sector.
+    if (do_bev) {
       const int T = a.tile_cells, tw = T >> 2;
       for (int w = tid; w < tw; w += FUSED_THREADS) tile[w] = 0u;
       __syncthreads();
-      for (long long B = E0 & ~3ll; B < E1; B += T) {
+      const long long Bfirst = E0 & ~7ll;
+      const int n_tiles = (int)((E1 - Bfirst + T - 1) / T);
+      const long long batches = (n + (long long)ENTRY_BATCH * FUSED_THREADS - 1) / ((long long)ENTRY_BATCH * FUSED_THREADS);
+      // what is left of the zero fill is spread over all compose batches of the frame
+      const long long left = (long long)(zend - zcur + FUSED_THREADS - 1) / FUSED_THREADS;
+      const int k3 = (batches && left > 0) ? (int)((left + batches * n_tiles - 1) / (batches * n_tiles)) : 0;
+      for (long long B = Bfirst; B < E1; B += T) {
         const long long lo = B > E0 ? B : E0, hi = B + T < E1 ? B + T : E1;
         const unsigned elo = (unsigned)(lo - E0), ehi = (unsigned)(hi - E0);
         const int shift = (int)(E0 - B);
         bool danger = false;
-#pragma unroll 8
-        for (long long i = tid; i < n; i += FUSED_THREADS) {
-          const unsigned e = my_entries[i];
-          if (e >= elo && e < ehi) danger |= tile_count(tile, (unsigned)((int)e + shift));
+        const unsigned span = ehi - elo;
+        // each thread re-reads the entries it wrote in S1 (L2 resident), ENTRY_BATCH loads in flight
+        for (long long i0 = 0; i0 < n; i0 += (long long)ENTRY_BATCH * FUSED_THREADS) {
+          unsigned e[ENTRY_BATCH];
+#pragma unroll
+          for (int u = 0; u < ENTRY_BATCH; ++u) {
+            const long long i = i0 + u * FUSED_THREADS + tid;
+            e[u] = i < n ? ld_u32_hint(my_entries + i, keep) : 0xFFFFFFFFu;
+          }
+          zf_pump(zbase, zcur, zend, k3);
+#pragma unroll
+          for (int u = 0; u < ENTRY_BATCH; ++u)
+            if (e[u] - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u] + shift));
         }
         if (danger) misc[3] = 1u;
+        // the zeros of this tile's cells must be on their way before its non-empty sectors
+        zf_until(zbase, zcur, zend, (int)(((hi + 3) >> 2) - ((E0 + 3) >> 2)));
         __syncthreads();
+        PROF_STAMP(4);
         if (misc[3]) {  // a byte may have wrapped: redo this tile with the exact (CAS) form
           __syncthreads();
           if (tid == 0) misc[3] = 0u;
           for (int w = tid; w < tw; w += FUSED_THREADS) tile[w] = 0u;
           __syncthreads();
           for (long long i = tid; i < n; i += FUSED_THREADS) {
-            const unsigned e = my_entries[i];
+            const unsigned e = __ldcg(my_entries + i);
             if (e >= elo && e < ehi) tile_count_exact(tile, (unsigned)((int)e + shift));
           }
           __syncthreads();
+          PROF_STAMP(5);
         }
-        float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
-        for (int w = tid; w < tw; w += FUSED_THREADS) {
-          const long long E = B + 4ll * w;
-          if (E >= hi) break;
-          const unsigned word = tile[w];
-          float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (word) {
-            tile[w] = 0u;
-            const unsigned c0 = word & 0xFFu, c1 = (word >> 8) & 0xFFu, c2 = (word >> 16) & 0xFFu, c3 = word >> 24;
-            val.x = lut[c0 < 64u ? c0 : 64u]; val.y = lut[c1 < 64u ? c1 : 64u];
-            val.z = lut[c2 < 64u ? c2 : 64u]; val.w = lut[c3 < 64u ? c3 : 64u];
-          }
-          if (E >= lo && E + 4 <= hi) {
-            __stcs(o4 + w, val);
-          } else {  // frame head / tail: only the cells of THIS frame
-            const float vv[4] = {val.x, val.y, val.z, val.w};
+        // scan the tile two words (8 cells = one 32-byte sector) at a time; only sectors with a
+        // non-empty cell are written (over the zero fill), and their tile words re-zeroed
+        {
+          const int rel_lo = (int)(lo - B), rel_hi = (int)(hi - B);
+          uint2* const tile2 = reinterpret_cast<uint2*>(tile);
+          float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
+          const int np = (rel_hi + 7) >> 3;
+#pragma unroll 4
+          for (int p = tid; p < np; p += FUSED_THREADS) {
+            const uint2 w = tile2[p];
+            if ((w.x | w.y) == 0u) continue;
+            tile2[p] = make_uint2(0u, 0u);
+            const float4 v0 = lut4(lut, w.x), v1 = lut4(lut, w.y);
+            const int c0 = p << 3;
+            if (c0 >= rel_lo && c0 + 8 <= rel_hi) {
+              __stcs(o4 + 2 * p, v0);
+              __stcs(o4 + 2 * p + 1, v1);
+            } else {  // frame head / tail: only the cells of THIS frame
+              const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              if (E + k >= lo && E + k < hi) a.bev[E + k] = vv[k];
+              for (int k = 0; k < 8; ++k)
+                if (c0 + k >= rel_lo && c0 + k < rel_hi && vv[k] != 0.f) a.bev[B + c0 + k] = vv[k];
+            }
           }
         }
         __syncthreads();
+        PROF_STAMP(6);
       }
+      zf_until(zbase, zcur, zend, zend);   // n == 0 and rounding leftovers
     }
   }
 }
@@ -300,9 +468,9 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   const long long cells = (long long)g.nbx * g.nby;
   int tile_words = 0;
   if (g.enable_bev) {
-    long long need = (cells + 3 + 3) / 4 + 1;        // whole frame incl. an unaligned head
-    tile_words = (int)(need < main_words_max() ? need : main_words_max());
-    tile_words &= ~3;                                 // tile_cells multiple of 16
+    long long need = ((cells + 7 + 3) / 4 + 3) & ~3ll;  // whole frame incl. an unaligned head (<= 7 cells)
+    const int cap = main_words_max() & ~3;
+    tile_words = (int)(need < cap ? need : cap);         // tile_cells multiple of 16
     if (tile_words < 4) tile_words = 4;
   }
   int main_words = g.enable_range ? g.H * g.W : 0;
@@ -317,6 +485,8 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.bev = (float*)out.bev;
   a.status = out.status; a.dropped = out.dropped;
   a.tile_cells = tile_words * 4;
+  a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
+  a.prof = fx.prof;
   const size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
   k_fused_sweep<<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
   ++*launches;

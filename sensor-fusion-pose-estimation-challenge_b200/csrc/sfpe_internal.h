@@ -61,6 +61,7 @@ struct FusedScratch {
   unsigned* queue;     // [grid][per_cta]
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
+  long long* prof;     // optional [grid][8] phase cycle accumulators
 };
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n);
 int fused_grid(int device, int n_frames);

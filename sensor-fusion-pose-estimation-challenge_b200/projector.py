@@ -80,6 +80,18 @@ class LidarProjector:
     def last_path(self):
         return self.lib.sfpe_last_path(self._ctx).decode()
 
+    PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo", "bev_write", "-")
+
+    def phase_profile(self, enable=True):
+        """Switch the fused kernel's per-phase SM-cycle counters on (and reset them) or off."""
+        _lib.check(self.lib.sfpe_phase_profile(self._ctx, int(bool(enable))), self._ctx)
+
+    def phase_cycles(self):
+        """dict phase -> SM cycles summed over all CTAs since phase_profile(True)."""
+        buf = (C.c_int64 * 8)()
+        _lib.check(self.lib.sfpe_phase_cycles(self._ctx, buf), self._ctx)
+        return dict(zip(self.PHASES, [int(v) for v in buf]))
+
     # ------------------------------------------------------------------ batched, device resident
     def alloc_outputs(self, n_frames, range_dtype="f32", range_layout="hwc", bev_dtype="f32",
                       winner=False, counts=False):
