@@ -176,7 +176,7 @@ def run_ours(a):
     host_all = np.concatenate([host] * reps)[: a.sweeps * a.n_pts] if reps > 1 else host
     pin_in = torch.from_numpy(host_all).pin_memory()
     d_pts = pin_in.to(dev, non_blocking=True)
-    pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path)
+    pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path, debug_flags=a.debug_flags)
     out = pr.alloc_outputs(a.sweeps)
     torch.cuda.synchronize()
 
@@ -306,6 +306,7 @@ def main():
     ap.add_argument("--e2e-chunk", type=int, default=32)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--debug-flags", type=int, default=0, help="kernel timing experiments (results invalid when non-zero)")
     ap.add_argument("--phases", action="store_true", help="also report the fused kernel's per-phase cycle shares")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup

@@ -184,6 +184,11 @@ SFPE_API const char* sfpe_last_path(const sfpe_ctx* ctx);
  * device and returns the sums over all CTAs: out8[0..7] = key init, point pass, deferred fp64
  * pass, range-scan resolve, BEV tile compose, BEV exact redo, BEV tile write, unused. */
 SFPE_API int sfpe_phase_profile(sfpe_ctx* ctx, int32_t enable);
+/* Self-test of the fused kernel's fp32 fast path on n packed float32 x,y,z,intensity points
+ * (device): out4[k] = largest deviation of the fp32 cell coordinate from its fp64 definition
+ * divided by the guard band that protects it (k = 0 azimuth column, 1 elevation row, 2 range
+ * bucket, 3 BEV bin).  A value < 1 means every fp32 decision taken was provably exact. */
+SFPE_API int sfpe_selftest_fastpath(sfpe_ctx* ctx, const float* d_xyzi, int64_t n, double* out4);
 SFPE_API int sfpe_phase_cycles(sfpe_ctx* ctx, int64_t* out8);
 
 #ifdef __cplusplus

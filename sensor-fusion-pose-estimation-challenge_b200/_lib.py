@@ -74,6 +74,7 @@ SIGNATURES = {
     "sfpe_last_path": (C.c_char_p, [C.c_void_p]),
     "sfpe_phase_profile": (C.c_int, [C.c_void_p, C.c_int32]),
     "sfpe_phase_cycles": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
+    "sfpe_selftest_fastpath": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_double)]),
 }
 
 _lib = None

@@ -117,6 +117,15 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
   g->inv_res_v_f = (float)(1.0 / g->res_rad_v);
   g->neg_x_min_f = (float)(-g->x_min);
   g->neg_y_min_f = (float)(-g->y_min);
+  if (g->enable_bev) {
+    // t = (v - start)/delta = v*inv + c0; guard = 3 ulp32 at the largest bin coordinate
+    g->bev_inv_x_f = (float)g->bev_inv_delta_x;
+    g->bev_inv_y_f = (float)g->bev_inv_delta_y;
+    g->bev_c0_x_f = (float)(-g->bev_start * g->bev_inv_delta_x);
+    g->bev_c0_y_f = (float)(-g->bev_start * g->bev_inv_delta_y);
+    g->bev_eps_x_f = 3.0f * (nextafterf((float)g->nex, INFINITY) - (float)g->nex);
+    g->bev_eps_y_f = 3.0f * (nextafterf((float)g->ney, INFINITY) - (float)g->ney);
+  }
   return SFPE_OK;
 }
 
@@ -284,6 +293,7 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.entries = (unsigned*)c->fused_buf;
     fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta;
     fs.frame0 = 0; fs.n_frames = n_frames;
+    fx.debug = c->params.reserved[0];
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;
     CK(c, launch_fused(g, src, fs, c->scratch, out, fx, st, &c->launches));
     c->last_path = "fused";
@@ -418,6 +428,19 @@ extern "C" int sfpe_phase_cycles(sfpe_ctx* c, int64_t* out8) {
     for (int b = 0; b < c->prof_grid; ++b)
       for (int i = 0; i < 8; ++i) out8[i] += h[b * 8 + i];
   free(h);
+  CK(c, e);
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_selftest_fastpath(sfpe_ctx* c, const float* d_xyzi, int64_t n, double* out4) {
+  if (!c || !out4 || n < 0 || (n > 0 && !d_xyzi) || ((uintptr_t)d_xyzi & 15)) return SFPE_ERR_INVALID_ARG;
+  CK(c, cudaSetDevice(c->device));
+  unsigned long long* d = nullptr;
+  CK(c, cudaMalloc((void**)&d, 4 * sizeof(unsigned long long)));
+  cudaError_t e = launch_selftest_fastpath(c->grid, d_xyzi, n, d, c->stream, &c->launches);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out4, d, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(d);
   CK(c, e);
   return SFPE_OK;
 }

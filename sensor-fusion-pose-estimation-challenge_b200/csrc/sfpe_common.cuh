@@ -35,6 +35,9 @@ struct DevGrid {
   double bev_inv_delta_x, bev_inv_delta_y;   // 1/delta (candidate bin only; edges decide)
   float inv_res_h_f, inv_res_v_f;            // 1/RES_RAD[1], 1/RES_RAD[0]
   float neg_x_min_f, neg_y_min_f;            // -X_MIN, -Y_MIN
+  // fp32 BEV candidate: t = v * bev_inv_f + bev_c0_f (in bins), guard band bev_eps_f bins
+  float bev_inv_x_f, bev_c0_x_f, bev_eps_x_f;
+  float bev_inv_y_f, bev_c0_y_f, bev_eps_y_f;
 };
 
 struct PointSrc {
@@ -159,29 +162,83 @@ __device__ __forceinline__ int bev_bin_f64(double v, double start, double delta,
 }
 
 // ---- fast path helpers (fused kernel) -------------------------------------------------
-// Guard bands of the fp32 cell computation: a point whose fp32 cell coordinate lies within
-// EPS of a (non-zero) integer is re-done in fp64.  Bounds: atan2f/asinf <= 2 ulp (CUDA math
-// API), one fp32 division and one fma -> |xi32 - xi64| < 2.6e-4 cells, |yi32 - yi64| < 3e-5
-// cells for |z/rho| < 0.95 ("fp32 fast path"); sfpe_selftest_fastpath measures it.
+// The fused kernel decides every cell index in fp32 and PROVES the decision with a guard band:
+// a point whose fp32 cell coordinate lies within EPS of a cell boundary (or outside the safe
+// domain of the approximations) is re-done with the fp64 functions above.  Error budgets (the
+// device self-test sfpe_selftest_fastpath measures the real deviations, tests/ assert them):
+//   column  xi = atan2(-y,x)/res_h - X_MIN:  polynomial 1.3e-7 rad + quotient 1.8e-7 + quadrant
+//           constants/rounding 2.5e-7 = 5.6e-7 rad = 1.6e-4 cells, + fma rounding and 1/res_h
+//           1.1e-4 cells  -> < 3e-4 cells,  EPS_COL = 1e-3
+//   row     yi = asin(z/rho)/res_v - Y_MIN, |z/rho| <= 0.55:  < 3e-5 cells, EPS_ROW = 2.5e-4
+//   range   t = 64*rho: relative 4e-7 -> guard 1e-6*t + 1e-3 buckets
+//   BEV     t = (v+R)/delta: < 1.5 ulp32(number of bins) -> guard 3 ulp32 (host: bev_eps_f)
 constexpr float EPS_COL = 1.0e-3f;
 constexpr float EPS_ROW = 2.5e-4f;
-constexpr float MAX_SIN_EL = 0.95f;
+constexpr float MAX_SIN_EL = 0.55f;
 
-// fp32 range-scan cell.  Returns true when (row, col) is PROVEN equal to the fp64 result and
-// inside the image; false -> the caller must use range_cell_f64.
-__device__ __forceinline__ bool range_cell_fast(const DevGrid& g, float x, float y, float z, float rho32, int& row,
-                                                int& col) {
-  const float xi = fmaf(atan2f(-y, x), g.inv_res_h_f, g.neg_x_min_f);
-  const float q = z / rho32;
-  const float yi = fmaf(asinf(q), g.inv_res_v_f, g.neg_y_min_f);
+// atan2(yy, xx) in (-pi, pi]: octant reduction to t = min/max in [0,1], odd minimax polynomial
+// (degree 15, fitted for abs error 1.3e-7 incl. fp32 Horner evaluation).  0/0, inf/inf and NaN
+// give NaN, which every guard test below rejects.
+__device__ __forceinline__ float atan2_fast(float yy, float xx) {
+  const float ax = fabsf(xx), ay = fabsf(yy);
+  const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+  const float t = __fdividef(mn, mx);
+  const float s = t * t;
+  float p = -0.004054493270814419f;
+  p = fmaf(p, s, 0.021862683817744255f);
+  p = fmaf(p, s, -0.055911920964717865f);
+  p = fmaf(p, s, 0.09642166644334793f);
+  p = fmaf(p, s, -0.13908617198467255f);
+  p = fmaf(p, s, 0.19946563243865967f);
+  p = fmaf(p, s, -0.33329859375953674f);
+  p = fmaf(p, s, 0.9999993443489075f);
+  float r = p * t;
+  if (ay > ax) r = 1.57079637f - r;
+  if (xx < 0.0f) r = 3.14159274f - r;
+  return copysignf(r, yy);
+}
+
+// asin(q) for |q| <= MAX_SIN_EL: odd minimax polynomial, abs error 8e-8 incl. evaluation.
+__device__ __forceinline__ float asin_fast(float q) {
+  const float s = q * q;
+  float p = 0.05534907057881355f;
+  p = fmaf(p, s, 0.014851636253297329f);
+  p = fmaf(p, s, 0.047862760722637177f);
+  p = fmaf(p, s, 0.07468582689762115f);
+  p = fmaf(p, s, 0.16667962074279785f);
+  p = fmaf(p, s, 0.9999998211860657f);
+  return p * q;
+}
+
+// fp32 cell coordinates (before truncation) of the range scan: xi (column), yi (row);
+// q = z/rho as computed from rs = rsqrt(x^2+y^2+z^2).
+__device__ __forceinline__ void range_coords_fast(const DevGrid& g, float x, float y, float z, float rs, float& xi,
+                                                  float& yi, float& q) {
+  xi = fmaf(atan2_fast(-y, x), g.inv_res_h_f, g.neg_x_min_f);
+  q = z * rs;
+  yi = fmaf(asin_fast(q), g.inv_res_v_f, g.neg_y_min_f);
+}
+
+// Returns true when (row, col) = trunc(yi), trunc(xi) is PROVEN equal to the fp64 result and
+// inside the image; false -> the caller must use range_cell_f64.  Cell boundaries under
+// truncation toward zero are the NON-ZERO integers.  Written so that NaN anywhere gives false.
+__device__ __forceinline__ bool range_cell_decide(const DevGrid& g, float xi, float yi, float q, int& row, int& col) {
   const float cx = rintf(xi), cy = rintf(yi);
-  // trunc-toward-zero semantics: the cell boundaries are the NON-ZERO integers
   const bool near_x = fabsf(xi - cx) <= EPS_COL && cx != 0.0f;
   const bool near_y = fabsf(yi - cy) <= EPS_ROW && cy != 0.0f;
   col = (int)xi;
   row = (int)yi;
-  // written so that NaN anywhere gives false
-  return !near_x && !near_y && fabsf(q) < MAX_SIN_EL && xi > -0.5f && yi > -0.5f && col < g.W && row < g.H;
+  return !near_x && !near_y && fabsf(q) <= MAX_SIN_EL && xi > -0.5f && yi > -0.5f && col < g.W && row < g.H;
+}
+
+// fp32 BEV bin candidate with guard band; -2 = undecided (caller uses bev_bin_f64, which also
+// handles the out-of-range / last-edge / NaN cases).
+__device__ __forceinline__ int bev_bin_f32(float v, float inv, float c0, float eps, int n_bins) {
+  const float t = fmaf(v, inv, c0);
+  const float fl = floorf(t);
+  const float fr = t - fl;
+  const bool ok = fr > eps && fr < 1.0f - eps && t > 0.0f && t < (float)n_bins;   // NaN -> false
+  return ok ? (int)fl : -2;
 }
 
 // BEV bin with one fp64 multiply for the candidate and the exact np.arange edges for the

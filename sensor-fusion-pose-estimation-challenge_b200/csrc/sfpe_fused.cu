@@ -24,13 +24,13 @@
 
 namespace sfpe {
 
-constexpr int FUSED_THREADS = 1024;
+constexpr int FUSED_THREADS = 640;
 constexpr int IDX_BITS32 = 18;                       // point index bits of the 32-bit key
 constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
 constexpr int SMEM_MISC_WORDS = 128;                 // LUT (65 floats) + counters
-constexpr int ENTRY_BATCH = 16;                      // entry loads in flight per thread (S2 compose)
+constexpr int ENTRY_BATCH = 8;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
 // ---- L2 residency hints: the entry list is written once and read once per BEV tile
@@ -64,10 +64,11 @@ __device__ __forceinline__ double rho_of_f4(const float4 v) {
 
 // Exact settlement of equal-prefix keys in shared memory; same algorithm as
 // settle_collision() in sfpe_generic.cu (champion = best point seen under (rho fp64, index)).
+// Rare path: the exact fp64 ranges are recomputed here from the points.
 __device__ __noinline__ void settle32(const float4* __restrict__ frame_pts, unsigned* addr, unsigned my_key,
-                                      double my_rho, unsigned my_idx, unsigned old_key) {
-  unsigned champ_key = my_key, champ_idx = my_idx;
-  double champ_rho = my_rho;
+                                      unsigned old_key) {
+  unsigned champ_key = my_key, champ_idx = my_key & IDX_MASK32;
+  double champ_rho = rho_of_f4(__ldg(frame_pts + champ_idx));
   {
     const unsigned oi = old_key & IDX_MASK32;
     const double orho = rho_of_f4(__ldg(frame_pts + oi));
@@ -84,11 +85,23 @@ __device__ __noinline__ void settle32(const float4* __restrict__ frame_pts, unsi
   }
 }
 
-__device__ __forceinline__ void key_min32(const float4* frame_pts, unsigned* keys, int cell, double rho, unsigned idx) {
+// qrho = quant_rho(fp64 rho) exactly (computed in fp32 with a guard band, or in fp64)
+__device__ __forceinline__ void key_min32(const float4* frame_pts, unsigned* keys, int cell, unsigned qrho, unsigned idx) {
   unsigned* addr = keys + cell;
-  const unsigned key = pack_key32(rho, idx);
+  const unsigned key = (qrho << IDX_BITS32) | idx;
   const unsigned old = atomicMin(addr, key);
-  if (old != KEY32_EMPTY && ((old ^ key) >> IDX_BITS32) == 0) settle32(frame_pts, addr, key, rho, idx, old);
+  if (old != KEY32_EMPTY && ((old ^ key) >> IDX_BITS32) == 0) settle32(frame_pts, addr, key, old);
+}
+
+// quant_rho from the fp32 range rho32 = s*rsqrt(s) (relative error < 4e-7) when the result is
+// provably the same as quant_rho(fp64 rho); otherwise from the exact fp64 range.
+__device__ __forceinline__ unsigned quant_rho_guarded(const float4 v, float rho32) {
+  const float t = rho32 * 64.0f;
+  const float fl = floorf(t);
+  const float fr = t - fl;
+  const float gq = fmaf(t, 1.0e-6f, 1.0e-3f);
+  if (fr > gq && fr < 1.0f - gq && t < 16382.0f) return (unsigned)fl;   // NaN -> exact path
+  return quant_rho(rho_of_f4(v));
 }
 
 // Saturating u8 count inside a packed word (any count >= 63 renders as 255, so 128..255 are
@@ -113,21 +126,22 @@ __device__ __forceinline__ void tile_count_exact(unsigned* tile, unsigned r) {
   }
 }
 
-// Zero-fill pump: up to `cnt` 16-byte zero stores of this thread's share of the frame's BEV
-// (word `cur`, then cur + FUSED_THREADS, ...).  Streaming (evict-first) stores.
-__device__ __forceinline__ void zf_pump(float4* __restrict__ zbase, int& cur, const int end, const int cnt) {
-  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 4
-  for (int u = 0; u < cnt; ++u) {
-    if (cur < end) __stcs(zbase + cur, z);
-    cur += FUSED_THREADS;
-  }
-}
-__device__ __forceinline__ void zf_until(float4* __restrict__ zbase, int& cur, const int end, const int upto) {
-  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-  const int lim = upto < end ? upto : end;
-#pragma unroll 4
-  for (; cur < lim; cur += FUSED_THREADS) __stcs(zbase + cur, z);
+// ---- warp roles.  The last STORE_WARPS warps of the CTA do nothing but stream the zeros of
+// the CTA's BEV frames (the per-SM store path, 32 B/clk, is the longest single resource of a
+// sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
+// the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
+constexpr int STORE_WARPS = 4;
+constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
+constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
+constexpr unsigned FILL_PERIOD0 = 500000u;            // assumed frame period (SM cycles) until one is measured
+
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+__device__ __forceinline__ uint4 ld_u32x4_hint(const uint4* ptr, unsigned long long pol) {
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
+  return v;
 }
 
 __device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
@@ -150,6 +164,7 @@ struct FusedArgs {
   int* status; int* dropped;
   int tile_cells;      // BEV cells per shared-memory tile (multiple of 16)
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
+  int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
 };
 
 // phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph`
@@ -168,91 +183,143 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   unsigned* const keys = smem;   // S0..S1c : H*W winner keys
   unsigned* const tile = smem;   // S2      : packed u8 BEV counts
   float* const lut = reinterpret_cast<float*>(smem + main_words);
-  unsigned* const misc = smem + main_words + 72;  // [0] deferred count, [1] status bits, [2] dropped, [3] tile redo flag
+  // misc: [0] deferred count, [1] status bits, [2] dropped, [3] tile redo flag,
+  //       [4] zero-fill progress: += 1 per store warp per finished frame, [5] frames begun by the compute warps,
+  //       [6] last frame period of the compute warps in SM cycles
+  unsigned* const misc = smem + main_words + 72;
   const int tid = threadIdx.x;
   const int hw = g.H * g.W;
   const long long cells = (long long)g.nbx * g.nby;
+  const bool do_bev = g.enable_bev && a.bev;
+  const int f_begin = a.fs.frame0 + blockIdx.x, f_end = a.fs.frame0 + a.fs.n_frames;
+  if (tid < 65) lut[tid] = (float)a.lut64[tid];
+  if (tid < 8) misc[tid] = 0u;
+  __syncthreads();   // the only CTA-wide barrier: the roles part here
+
+  // ======================================================================== zero-fill warps
+  if (tid >= CT) {
+    if (!do_bev) return;
+    if (a.debug & 1) { if ((tid & 31) == 0) atomicAdd(&misc[4], 0x10000000u); return; }
+    const int st = tid - CT;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    unsigned k = 0;
+    for (int f = f_begin; f < f_end; f += gridDim.x, ++k) {
+      // at most one frame ahead of the compute warps: the fill of frame k runs next to the
+      // rasterisation of frame k-1 (an unbounded run-ahead would saturate HBM with zeros first
+      // and starve the point pass of every SM)
+      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(500);
+      // this frame's BEV is cells [E0, E1) of a.bev: full 16-byte words [W0, W1) + head / tail cells
+      const long long E0 = (long long)f * cells, E1 = E0 + cells;
+      const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
+      if (st < 8) {   // head cells [E0, 4*W0) and tail cells [4*W1, E1), clipped to the frame
+        const long long c = st < 4 ? E0 + st : 4 * W1 + (st - 4);
+        const bool mine = st < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
+        if (mine) a.bev[c] = 0.f;
+      }
+      float4* p = reinterpret_cast<float4*>(a.bev) + W0 + st;
+      long long left = W1 - W0 - st;   // words from p to the end of the frame
+      // Paced: the frame's zeros are spread over ~85 % of one frame period of the compute warps
+      // (misc[6], measured by them; FILL_PERIOD0 before the first measurement), one group of
+      // 8 x 128 16-byte stores at a time.  A burst at the full 32 B/clk of the store path would
+      // fill the LSU queue in front of the compute warps' own loads / stores and, because every
+      // SM does the same at the same time, saturate HBM with zeros while the point pass starves.
+      const long long groups = (W1 - W0 + 8 * ST - 1) / (8 * ST);
+      const unsigned period = *reinterpret_cast<volatile unsigned*>(&misc[6]);
+      const long long interval = groups > 0 ? ((long long)(period ? period : FILL_PERIOD0) * 27 >> 5) / groups : 0;
+      long long t_next = clock64();
+      for (; left > 7 * ST; left -= 8 * ST, p += 8 * ST) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) __stcs(p + u * ST, z);
+        t_next += interval;
+        while (clock64() < t_next) __nanosleep(64);
+      }
+      for (; left > 0; left -= ST, p += ST) __stcs(p, z);
+      __threadfence_block();
+      __syncwarp();
+      if ((tid & 31) == 0) atomicAdd(&misc[4], 1u);
+    }
+    return;
+  }
+
+  // ======================================================================== compute warps
   unsigned* const my_entries = a.entries + (size_t)blockIdx.x * a.per_cta;
   unsigned* const my_queue = a.queue + (size_t)blockIdx.x * a.per_cta;
   const float height_bg = (float)g.height_bg;
   const unsigned cells_m1 = (unsigned)(cells - 1);
   const unsigned long long keep = l2_policy_evict_last();
-  const bool do_bev = g.enable_bev && a.bev;
-  if (tid < 65) lut[tid] = (float)a.lut64[tid];
   long long t_prev = clock64();
+  unsigned frames_done = 0;
+  long long t_frame = 0;
 
-  for (int f = a.fs.frame0 + blockIdx.x; f < a.fs.frame0 + a.fs.n_frames; f += gridDim.x) {
+  for (int f = f_begin; f < f_end; f += gridDim.x, ++frames_done) {
     long long base, n;
     frame_span(a.fs, f, base, n);
     const float4* __restrict__ fp = a.pts + base;
-
-    // ---- ZF set-up: this frame's BEV is cells [E0, E1) of a.bev; full 16-byte words
-    // [W0, W1) are zero-filled by the pump, the (<= 3 + 3) head / tail cells right here.
     const long long E0 = (long long)f * cells, E1 = E0 + cells;
-    float4* zbase = nullptr;
-    int zcur = tid, zend = 0;
-    if (do_bev) {
-      const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
-      zbase = reinterpret_cast<float4*>(a.bev) + W0;
-      zend = W1 > W0 ? (int)(W1 - W0) : 0;
-      if (tid < 8) {   // head cells [E0, 4*W0) and tail cells [4*W1, E1), clipped to the frame
-        const long long c = tid < 4 ? E0 + tid : 4 * W1 + (tid - 4);
-        const bool mine = tid < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
-        if (mine) a.bev[c] = 0.f;
-      }
-    }
-    const int zper = (zend + FUSED_THREADS - 1) / FUSED_THREADS;   // zero stores per thread per frame
 
     // ---- S0
     if (g.enable_range)
-      for (int i = tid; i < hw; i += FUSED_THREADS) keys[i] = KEY32_EMPTY;
+      for (int i = tid; i < hw; i += CT) keys[i] = KEY32_EMPTY;
     if (tid < 4) misc[tid] = 0u;
-    __syncthreads();
+    if (tid == 0) {
+      misc[5] = frames_done + 1;   // lets the zero-fill warps start on the next frame
+      const long long now = clock64();
+      if (frames_done) misc[6] = (unsigned)min(now - t_frame, 0x7FFFFFFFll);   // frame period for the fill pacing
+      t_frame = now;
+    }
+    // the first two S1 iterations of points are pulled into L2 while the keys are initialised
+    for (long long l = tid; l * 8 < n && l < 2 * (4 * CT / 8); l += CT) prefetch_l2(fp + l * 8);
+    compute_sync();
     PROF_STAMP(0);
 
-    // ---- S1: one pass over the points (+ ~5/8 of the zero fill)
-    {
-      const long long iters = (n + 4 * FUSED_THREADS - 1) / (4 * FUSED_THREADS);
-      const int k1 = iters ? (int)((((long long)zper * 5 >> 3) + iters - 1) / iters) : 0;
-      for (long long i0 = 0; i0 < n; i0 += 4 * FUSED_THREADS) {
-        float4 v[4];
+    // ---- S1: one pass over the points
+    for (long long i0 = 0; i0 < n; i0 += 4 * CT) {
+      float4 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long i = i0 + u * FUSED_THREADS + tid;
-          if (i < n) v[u] = __ldg(fp + i);
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * CT + tid;
+        if (i < n) v[u] = __ldg(fp + i);
+      }
+      {  // L2 prefetch two iterations ahead (one 128-byte line = 8 points per thread)
+        const long long l = i0 + 2 * 4 * CT + (long long)tid * 8;
+        if (tid < 4 * CT / 8 && l < n && !(a.debug & 64)) prefetch_l2(fp + l);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long i = i0 + u * CT + tid;
+        if (i >= n) continue;
+        const float x = v[u].x, y = v[u].y, z = v[u].z;
+        if (g.enable_bev) {
+          int bx = bev_bin_f32(x, g.bev_inv_x_f, g.bev_c0_x_f, g.bev_eps_x_f, g.nbx);
+          int by = bev_bin_f32(y, g.bev_inv_y_f, g.bev_c0_y_f, g.bev_eps_y_f, g.nby);
+          if (bx == -2) bx = bev_bin_f64((double)x, g.bev_start, g.bev_delta_x, g.nex);
+          if (by == -2) by = bev_bin_f64((double)y, g.bev_start, g.bev_delta_y, g.ney);
+          // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
+          const unsigned e = (bx >= 0 && by >= 0) ? cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) : 0xFFFFFFFFu;
+          if (!(a.debug & 16)) st_u32_hint(my_entries + i, e, keep);
         }
-        zf_pump(zbase, zcur, zend, k1);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const long long i = i0 + u * FUSED_THREADS + tid;
-          if (i >= n) continue;
-          if (g.enable_bev) {
-            const int bx = bev_bin_fast((double)v[u].x, g.bev_start, g.bev_delta_x, g.bev_inv_delta_x, g.nex);
-            const int by = bev_bin_fast((double)v[u].y, g.bev_start, g.bev_delta_y, g.bev_inv_delta_y, g.ney);
-            // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
-            st_u32_hint(my_entries + i,
-                        (bx >= 0 && by >= 0) ? cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) : 0xFFFFFFFFu,
-                        keep);
-          }
-          if (g.enable_range) {
-            const double rho = rho_of_f4(v[u]);
-            int row, col;
-            if (range_cell_fast(g, v[u].x, v[u].y, v[u].z, (float)rho, row, col)) {
-              key_min32(fp, keys, row * g.W + col, rho, (unsigned)i);
-            } else {
-              my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
-            }
+        if (g.enable_range) {
+          const float s = fmaf(z, z, fmaf(y, y, x * x));
+          const float rs = rsqrtf(s);
+          float xi, yi, q;
+          range_coords_fast(g, x, y, z, rs, xi, yi, q);
+          int row, col;
+          if (range_cell_decide(g, xi, yi, q, row, col)) {
+            if (a.debug & 32) { if (row * g.W + col == -77) keys[0] = 0; } else
+            key_min32(fp, keys, row * g.W + col, quant_rho_guarded(v[u], s * rs), (unsigned)i);
+          } else {
+            my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
           }
         }
       }
     }
-    __syncthreads();
+    compute_sync();
     PROF_STAMP(1);
 
     if (g.enable_range) {
       // ---- S1b: deferred points, full fp64 (guard band, image border, wrap, NaN, errors)
       const unsigned qn = misc[0];
-      for (unsigned j = tid; j < qn; j += FUSED_THREADS) {
+      for (unsigned j = tid; j < qn; j += CT) {
         const unsigned i = my_queue[j];
         const float4 v = __ldg(fp + i);
         Pt p; p.x = v.x; p.y = v.y; p.z = v.z; p.it = v.w;
@@ -263,10 +330,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           atomicOr(&misc[1], (unsigned)err);
           atomicAdd(&misc[2], 1u);
         } else {
-          key_min32(fp, keys, row * g.W + col, rho, i);
+          key_min32(fp, keys, row * g.W + col, quant_rho(rho), i);
         }
       }
-      __syncthreads();
+      compute_sync();
       PROF_STAMP(2);
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
@@ -278,56 +345,65 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         // Task (k, r) = k-th aligned group of 4 flat output cells whose first cell lies in output
         // row r; tasks run k-major / r-minor, so a warp (H = 32: one lane per row) gathers the
         // winners of ~4 neighbouring columns -- neighbouring points of a firing-order sweep.
+        // Pass A only prefetches every winner into L2 (no register, nothing waits); pass B gathers.
         const int kmax = ((g.W + 3) >> 2) + 1;
         const int ntask = kmax * g.H;
-        const int k2 = (int)(((long long)(zper >> 3) * FUSED_THREADS + ntask - 1) / ntask);
-        for (int t = tid; t < ntask; t += FUSED_THREADS) {
-          const int k = t / g.H, r = t - k * g.H;
-          const int gid = ((r * g.W + 3) >> 2) + k;
-          zf_pump(zbase, zcur, zend, k2);
-          if (gid >= (((r + 1) * g.W + 3) >> 2)) continue;
-          const int c = gid << 2;
-          int orow = r, col = c - r * g.W;
-          unsigned key[4];
+#pragma unroll 1
+        for (int pass = (a.debug & 8) ? 1 : 0; pass < 2; ++pass) {
+          for (int t = tid; t < ntask; t += CT) {
+            const int k = t / g.H, r = t - k * g.H;
+            const int gid = ((r * g.W + 3) >> 2) + k;
+            if (gid >= (((r + 1) * g.W + 3) >> 2)) continue;
+            const int c = gid << 2;
+            int orow = r, col = c - r * g.W;
+            unsigned key[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            key[j] = keys[(g.H - 1 - orow) * g.W + col];
-            if (++col == g.W) { col = 0; ++orow; }
-          }
-          float4 v[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (key[j] != KEY32_EMPTY) v[j] = __ldg(fp + (key[j] & IDX_MASK32));
-          float d[4], h[4], it[4];
-          int win[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
-            if (key[j] != KEY32_EMPTY) {
-              win[j] = (int)(key[j] & IDX_MASK32);
-              const double x = v[j].x, y = v[j].y;
-              d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
-              h[j] = v[j].z; it[j] = v[j].w;
+            for (int j = 0; j < 4; ++j) {
+              key[j] = keys[(g.H - 1 - orow) * g.W + col];
+              if (++col == g.W) { col = 0; ++orow; }
             }
-          }
-          if (a.range) {
-            if (a.range_layout == 0) {
-              float* o = a.range + (size_t)f * 3 * hw + c;
-              __stcs(reinterpret_cast<float4*>(o), make_float4(d[0], d[1], d[2], d[3]));
-              __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
-              __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
-            } else {
-              float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
-              __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
-              __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
-              __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
+            if (pass == 0) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (key[j] != KEY32_EMPTY) prefetch_l2(fp + (key[j] & IDX_MASK32));
+              continue;
             }
+            float4 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (key[j] != KEY32_EMPTY) v[j] = (a.debug & 4) ? make_float4(1.f, 2.f, 3.f, (float)key[j]) : __ldg(fp + (key[j] & IDX_MASK32));
+            float d[4], h[4], it[4];
+            int win[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
+              if (key[j] != KEY32_EMPTY) {
+                win[j] = (int)(key[j] & IDX_MASK32);
+                const double x = v[j].x, y = v[j].y;
+                d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
+                h[j] = v[j].z; it[j] = v[j].w;
+              }
+            }
+            if (a.debug & 2) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
+            if (a.range) {
+              if (a.range_layout == 0) {
+                float* o = a.range + (size_t)f * 3 * hw + c;
+                __stcs(reinterpret_cast<float4*>(o), make_float4(d[0], d[1], d[2], d[3]));
+                __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
+                __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
+              } else {
+                float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
+                __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
+                __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
+                __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
+              }
+            }
+            if (a.winner)
+              __stcs(reinterpret_cast<int4*>(a.winner + (size_t)f * hw + c), make_int4(win[0], win[1], win[2], win[3]));
           }
-          if (a.winner)
-            __stcs(reinterpret_cast<int4*>(a.winner + (size_t)f * hw + c), make_int4(win[0], win[1], win[2], win[3]));
         }
       } else {
-        for (int c = tid; c < hw; c += FUSED_THREADS) {
+        for (int c = tid; c < hw; c += CT) {
           const int orow = c / g.W, col = c - orow * g.W;
           const unsigned key = keys[(g.H - 1 - orow) * g.W + col];
           float d = 0.f, h = height_bg, it = 0.f;
@@ -351,7 +427,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           if (a.winner) __stcs(a.winner + (size_t)f * hw + c, win);
         }
       }
-      __syncthreads();
+      compute_sync();
       PROF_STAMP(3);
     } else if (tid == 0) {
       if (a.status) a.status[f] = 0;
@@ -361,48 +437,59 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     // ---- S2: BEV, one flat tile of the output at a time.  Tiles start on a 32-byte sector.
     if (do_bev) {
       const int T = a.tile_cells, tw = T >> 2;
-      for (int w = tid; w < tw; w += FUSED_THREADS) tile[w] = 0u;
-      __syncthreads();
-      const long long Bfirst = E0 & ~7ll;
-      const int n_tiles = (int)((E1 - Bfirst + T - 1) / T);
-      const long long batches = (n + (long long)ENTRY_BATCH * FUSED_THREADS - 1) / ((long long)ENTRY_BATCH * FUSED_THREADS);
-      // what is left of the zero fill is spread over all compose batches of the frame
-      const long long left = (long long)(zend - zcur + FUSED_THREADS - 1) / FUSED_THREADS;
-      const int k3 = (batches && left > 0) ? (int)((left + batches * n_tiles - 1) / (batches * n_tiles)) : 0;
-      for (long long B = Bfirst; B < E1; B += T) {
+      for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+      compute_sync();
+      const uint4* const entries4 = reinterpret_cast<const uint4*>(my_entries);
+      const long long n4 = (n + 3) >> 2;
+      for (long long B = E0 & ~7ll; B < E1; B += T) {
         const long long lo = B > E0 ? B : E0, hi = B + T < E1 ? B + T : E1;
         const unsigned elo = (unsigned)(lo - E0), ehi = (unsigned)(hi - E0);
+        const unsigned span = ehi - elo;
         const int shift = (int)(E0 - B);
         bool danger = false;
-        const unsigned span = ehi - elo;
-        // each thread re-reads the entries it wrote in S1 (L2 resident), ENTRY_BATCH loads in flight
-        for (long long i0 = 0; i0 < n; i0 += (long long)ENTRY_BATCH * FUSED_THREADS) {
-          unsigned e[ENTRY_BATCH];
+        // the entry list of S1 (L2 resident), 16 bytes = 4 entries per load, ENTRY_BATCH loads in flight
+        for (long long q0 = 0; q0 < n4; q0 += (long long)ENTRY_BATCH * CT) {
+          uint4 e[ENTRY_BATCH];
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            const long long i = i0 + u * FUSED_THREADS + tid;
-            e[u] = i < n ? ld_u32_hint(my_entries + i, keep) : 0xFFFFFFFFu;
+            const long long q = q0 + u * CT + tid;
+            e[u] = q < n4 ? ld_u32x4_hint(entries4 + q, keep) : make_uint4(~0u, ~0u, ~0u, ~0u);
           }
-          zf_pump(zbase, zcur, zend, k3);
 #pragma unroll
-          for (int u = 0; u < ENTRY_BATCH; ++u)
-            if (e[u] - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u] + shift));
+          for (int u = 0; u < ENTRY_BATCH; ++u) {
+            const long long q = q0 + u * CT + tid;
+            if (4 * q + 4 > n) {   // last word of the list: slots past n hold stale entries
+              const long long m = n - 4 * q;
+              if (m < 2) e[u].y = ~0u;
+              if (m < 3) e[u].z = ~0u;
+              if (m < 4) e[u].w = ~0u;
+              if (m < 1) e[u].x = ~0u;
+            }
+            if (e[u].x - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].x + shift));
+            if (e[u].y - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].y + shift));
+            if (e[u].z - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].z + shift));
+            if (e[u].w - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].w + shift));
+          }
         }
         if (danger) misc[3] = 1u;
-        // the zeros of this tile's cells must be on their way before its non-empty sectors
-        zf_until(zbase, zcur, zend, (int)(((hi + 3) >> 2) - ((E0 + 3) >> 2)));
-        __syncthreads();
+        // the zeros of this frame must have been issued before its non-empty sectors go out
+        if (tid == 0) {
+          const unsigned want = (unsigned)STORE_WARPS * (frames_done + 1);
+          while (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) __nanosleep(200);
+          __threadfence_block();
+        }
+        compute_sync();
         PROF_STAMP(4);
         if (misc[3]) {  // a byte may have wrapped: redo this tile with the exact (CAS) form
-          __syncthreads();
+          compute_sync();
           if (tid == 0) misc[3] = 0u;
-          for (int w = tid; w < tw; w += FUSED_THREADS) tile[w] = 0u;
-          __syncthreads();
-          for (long long i = tid; i < n; i += FUSED_THREADS) {
+          for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+          compute_sync();
+          for (long long i = tid; i < n; i += CT) {
             const unsigned e = __ldcg(my_entries + i);
             if (e >= elo && e < ehi) tile_count_exact(tile, (unsigned)((int)e + shift));
           }
-          __syncthreads();
+          compute_sync();
           PROF_STAMP(5);
         }
         // scan the tile two words (8 cells = one 32-byte sector) at a time; only sectors with a
@@ -413,7 +500,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
           const int np = (rel_hi + 7) >> 3;
 #pragma unroll 4
-          for (int p = tid; p < np; p += FUSED_THREADS) {
+          for (int p = tid; p < np; p += CT) {
             const uint2 w = tile2[p];
             if ((w.x | w.y) == 0u) continue;
             tile2[p] = make_uint2(0u, 0u);
@@ -430,10 +517,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             }
           }
         }
-        __syncthreads();
+        compute_sync();
         PROF_STAMP(6);
       }
-      zf_until(zbase, zcur, zend, zend);   // n == 0 and rounding leftovers
     }
   }
 }
@@ -487,8 +573,53 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.tile_cells = tile_words * 4;
   a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
   a.prof = fx.prof;
+  a.debug = fx.debug;
   const size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
   k_fused_sweep<<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Self-test of the fp32 fast path: largest deviation of each fp32 cell coordinate from its fp64
+// definition over a point set, as a FRACTION of the guard band that protects it (< 1 means the
+// guard band holds; the tests want < 0.5).  out[0] column, [1] row, [2] range bucket, [3] BEV.
+__global__ void __launch_bounds__(256) k_selftest_fastpath(const __grid_constant__ DevGrid g, const float4* __restrict__ pts,
+                                                           long long n, unsigned long long* out) {
+  double m[4] = {0.0, 0.0, 0.0, 0.0};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = __ldg(pts + i);
+    const float x = v.x, y = v.y, z = v.z;
+    const float s = fmaf(z, z, fmaf(y, y, x * x));
+    const float rs = rsqrtf(s);
+    float xi, yi, q;
+    range_coords_fast(g, x, y, z, rs, xi, yi, q);
+    Pt p; p.x = x; p.y = y; p.z = z; p.it = v.w;
+    const double rho = rho_of(p);
+    const double xi64 = __dsub_rn(__ddiv_rn(atan2(-p.y, p.x), g.res_rad_h), g.x_min);
+    const double yi64 = __dsub_rn(__ddiv_rn(asin(__ddiv_rn(p.z, rho)), g.res_rad_v), g.y_min);
+    if (xi64 == xi64 && yi64 == yi64 && fabsf(q) <= MAX_SIN_EL) {
+      m[0] = fmax(m[0], fabs((double)xi - xi64) / (double)EPS_COL);
+      m[1] = fmax(m[1], fabs((double)yi - yi64) / (double)EPS_ROW);
+    }
+    const float t = (s * rs) * 64.0f;
+    if (t < 16382.0f) m[2] = fmax(m[2], fabs((double)t - rho * 64.0) / (double)fmaf(t, 1.0e-6f, 1.0e-3f));
+    if (g.enable_bev) {
+      const float tx = fmaf(x, g.bev_inv_x_f, g.bev_c0_x_f), ty = fmaf(y, g.bev_inv_y_f, g.bev_c0_y_f);
+      if (tx > 0.f && tx < (float)g.nbx) m[3] = fmax(m[3], fabs((double)tx - ((double)x - g.bev_start) / g.bev_delta_x) / (double)g.bev_eps_x_f);
+      if (ty > 0.f && ty < (float)g.nby) m[3] = fmax(m[3], fabs((double)ty - ((double)y - g.bev_start) / g.bev_delta_y) / (double)g.bev_eps_y_f);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) atomicMax(out + k, (unsigned long long)__double_as_longlong(m[k]));
+}
+
+cudaError_t launch_selftest_fastpath(const DevGrid& g, const float* pts, long long n, unsigned long long* d_out4,
+                                     cudaStream_t st, long long* launches) {
+  cudaError_t e = cudaMemsetAsync(d_out4, 0, 4 * sizeof(unsigned long long), st);
+  if (e != cudaSuccess || n <= 0) return e;
+  k_selftest_fastpath<<<148 * 4, 256, 0, st>>>(g, reinterpret_cast<const float4*>(pts), n, d_out4);
   ++*launches;
   return cudaGetLastError();
 }

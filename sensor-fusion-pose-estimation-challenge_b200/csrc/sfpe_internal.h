@@ -62,10 +62,14 @@ struct FusedScratch {
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
   long long* prof;     // optional [grid][8] phase cycle accumulators
+  int debug;           // sfpe_params.reserved[0]: bit 0 = skip the BEV zero fill (timing experiments only)
 };
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n);
 int fused_grid(int device, int n_frames);
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
                          const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches);
+
+cudaError_t launch_selftest_fastpath(const DevGrid& g, const float* pts, long long n, unsigned long long* d_out4,
+                                     cudaStream_t st, long long* launches);
 
 }  // namespace sfpe

@@ -22,7 +22,7 @@ def _torch():
 
 class LidarProjector:
     def __init__(self, device=0, bev_res=(0.2, 0.2), max_range=120, enable_range=True, enable_bev=True,
-                 extrinsic=None, slice_edges=None, key_prefix_bits=0, path=0, **grid):
+                 extrinsic=None, slice_edges=None, key_prefix_bits=0, path=0, debug_flags=0, **grid):
         """bev_res = (res_y, res_x) like the reference's `res` tuple
         (birds_eye_view_generator.py:43 uses res[1] for x and res[0] for y)."""
         self.lib = _lib.load()
@@ -50,6 +50,7 @@ class LidarProjector:
             p.n_slices = len(se) - 1
             for i, v in enumerate(se):
                 p.slice_edges[i] = v
+        p.reserved[0] = int(debug_flags)
         p.key_prefix_bits = int(key_prefix_bits)
         p.path = int(path)
         self.params = p
@@ -91,6 +92,13 @@ class LidarProjector:
         buf = (C.c_int64 * 8)()
         _lib.check(self.lib.sfpe_phase_cycles(self._ctx, buf), self._ctx)
         return dict(zip(self.PHASES, [int(v) for v in buf]))
+
+    def selftest_fastpath(self, points):
+        """points: CUDA float32 (N,4) contiguous.  Returns the four guard-band utilisation
+        fractions (column, row, range bucket, BEV bin) of sfpe_selftest_fastpath."""
+        buf = (C.c_double * 4)()
+        _lib.check(self.lib.sfpe_selftest_fastpath(self._ctx, points.data_ptr(), int(points.shape[0]), buf), self._ctx)
+        return [float(v) for v in buf]
 
     # ------------------------------------------------------------------ batched, device resident
     def alloc_outputs(self, n_frames, range_dtype="f32", range_layout="hwc", bev_dtype="f32",

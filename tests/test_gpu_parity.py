@@ -272,3 +272,51 @@ def test_fused_equals_generic_on_bench_shape(pkg, synth):
     b = _run_batch(pkg, sweeps, ragged=False, path=1, counts=False)
     for k in ("range", "winner", "bev", "status", "dropped"):
         assert np.array_equal(a[k], b[k]), k
+
+
+# ---------------------------------------------------------------- fp32 fast path: guard bands hold
+def _adversarial_points(n, seed):
+    """Directions spread over the whole sphere band the fast path accepts, ranges from 0.3 m to
+    250 m, plus points placed right on range-scan cell boundaries and BEV bin edges."""
+    rng = np.random.default_rng(seed)
+    az = rng.uniform(-np.pi, np.pi, n)
+    el = np.deg2rad(rng.uniform(-33.0, 33.0, n))
+    r = np.exp(rng.uniform(np.log(0.3), np.log(250.0), n))
+    k = n // 4
+    az[:k] = (np.round(rng.uniform(0, 1800, k)) - 900.0) * lo.RES_RAD[1] + rng.normal(0, 2e-7, k)   # column boundaries
+    el[k:2 * k] = (np.round(rng.uniform(0, 31, k)) + lo.Y_MIN) * lo.RES_RAD[0] + rng.normal(0, 2e-7, k)  # row boundaries
+    p = np.empty((n, 4), np.float32)
+    p[:, 0] = r * np.cos(el) * np.cos(az)
+    p[:, 1] = -r * np.cos(el) * np.sin(az)
+    p[:, 2] = r * np.sin(el)
+    p[:, 3] = rng.uniform(0, 255, n)
+    e = np.arange(-120, 120, 0.2)
+    p[2 * k:3 * k, 0] = (e[rng.integers(0, len(e), k)] + rng.normal(0, 1e-5, k)).astype(np.float32)  # BEV x edges
+    p[2 * k:3 * k, 1] = (e[rng.integers(0, len(e), k)] + rng.normal(0, 1e-5, k)).astype(np.float32)  # BEV y edges
+    return p
+
+
+def test_fastpath_guard_bands_hold(pkg, synth):
+    import torch
+    pr = pkg.LidarProjector(device=0)
+    worst = np.zeros(4)
+    sets = [_adversarial_points(1 << 20, s) for s in range(4)] + [synth.make_sweep("vls128", seed=5, near_heavy=True)]
+    for p in sets:
+        worst = np.maximum(worst, pr.selftest_fastpath(torch.from_numpy(p).cuda()))
+    pr.close()
+    # deviation / guard band: < 1 is required for exactness, < 0.5 leaves a 2x margin
+    assert (worst < 0.5).all(), worst
+    assert worst.max() > 0.0
+
+
+def test_fused_path_adversarial_boundaries(pkg):
+    """Points sitting on cell boundaries: the guarded fp32 decisions and the fp64 re-dos together
+    must still give the oracle's cells and winners (in-FOV subset, so the reference would not raise)."""
+    p = _adversarial_points(200000, 11)
+    P = np.zeros((len(p), 5)); P[:, :4] = p
+    _, _, _, err = lo.front_view_cells(P)
+    sweeps = [p[err == 0][:150000], p[:100000]]
+    res = _run_batch(pkg, sweeps, path=2, counts=False)
+    assert res["_path"] == "fused"
+    for f, s in enumerate(sweeps):
+        _check_frame(res, f, s)
