@@ -287,11 +287,13 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.grid = fused_grid(c->device, n_frames);
     fx.per_cta = (max_n + 255) & ~255ll;
     if (fx.per_cta < 256) fx.per_cta = 256;
-    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * 2;
+    const FusedGeom geo = fused_geometry(g);
+    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 4);   // entry buckets + deferred queue + collision records
     const int grc = grow(c, &c->fused_buf, &c->fused_cap, need);
     if (grc) return grc;
     fx.entries = (unsigned*)c->fused_buf;
-    fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta;
+    fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta * geo.n_buckets;
+    fx.cqueue = fx.queue + (size_t)fx.grid * fx.per_cta;
     fs.frame0 = 0; fs.n_frames = n_frames;
     fx.debug = c->params.reserved[0];
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;

@@ -182,7 +182,9 @@ constexpr float MAX_SIN_EL = 0.55f;
 __device__ __forceinline__ float atan2_fast(float yy, float xx) {
   const float ax = fabsf(xx), ay = fabsf(yy);
   const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
-  const float t = __fdividef(mn, mx);
+  float rc;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(mx));   // 1 ulp; 0 -> inf -> NaN below, rejected by the guards
+  const float t = mn * rc;
   const float s = t * t;
   float p = -0.004054493270814419f;
   p = fmaf(p, s, 0.021862683817744255f);

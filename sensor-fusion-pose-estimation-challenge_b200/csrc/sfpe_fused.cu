@@ -30,7 +30,7 @@ constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
 constexpr int SMEM_MISC_WORDS = 128;                 // LUT (65 floats) + counters
-constexpr int ENTRY_BATCH = 8;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
+constexpr int ENTRY_BATCH = 2;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
 // ---- L2 residency hints: the entry list is written once and read once per BEV tile
@@ -62,35 +62,35 @@ __device__ __forceinline__ double rho_of_f4(const float4 v) {
   return __dsqrt_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)));
 }
 
-// Exact settlement of equal-prefix keys in shared memory; same algorithm as
-// settle_collision() in sfpe_generic.cu (champion = best point seen under (rho fp64, index)).
-// Rare path: the exact fp64 ranges are recomputed here from the points.
-__device__ __noinline__ void settle32(const float4* __restrict__ frame_pts, unsigned* addr, unsigned my_key,
-                                      unsigned old_key) {
-  unsigned champ_key = my_key, champ_idx = my_key & IDX_MASK32;
-  double champ_rho = rho_of_f4(__ldg(frame_pts + champ_idx));
-  {
-    const unsigned oi = old_key & IDX_MASK32;
-    const double orho = rho_of_f4(__ldg(frame_pts + oi));
-    if (better(orho, oi, champ_rho, champ_idx)) { champ_key = old_key; champ_rho = orho; champ_idx = oi; }
-  }
-  for (;;) {
-    const unsigned cur = *reinterpret_cast<volatile unsigned*>(addr);
-    if (cur == champ_key) return;
-    if ((cur & ~IDX_MASK32) < (champ_key & ~IDX_MASK32)) return;
-    const unsigned ci = cur & IDX_MASK32;
-    const double crho = rho_of_f4(__ldg(frame_pts + ci));
-    if (better(crho, ci, champ_rho, champ_idx)) return;
-    if (atomicCAS(addr, cur, champ_key) == cur) return;
+// Winner keys whose quantised range is equal are settled exactly, but not where they are found:
+// a point that meets an equal-prefix key at its atomicMin only records the two candidates (itself
+// and the previous holder) in a per-CTA collision list; after the point pass every recorded
+// candidate tries to install itself over the current holder under the exact order (rho fp64,
+// index).  The best candidate of the winning bucket ends up in the key whatever the schedule:
+// it replaces any worse holder (CAS, retried) and no worse candidate can replace it.  Every
+// point of a bucket that holds more than one point is recorded (the first one by the second).
+__device__ __forceinline__ void note_collision(uint2* __restrict__ cq, unsigned* misc, int cell, unsigned key, unsigned old) {
+  if (old != KEY32_EMPTY && ((old ^ key) >> IDX_BITS32) == 0) {
+    const unsigned pos = atomicAdd(&misc[7], 2u);
+    cq[pos] = make_uint2((unsigned)cell, key & IDX_MASK32);
+    cq[pos + 1] = make_uint2((unsigned)cell, old & IDX_MASK32);
   }
 }
 
-// qrho = quant_rho(fp64 rho) exactly (computed in fp32 with a guard band, or in fp64)
-__device__ __forceinline__ void key_min32(const float4* frame_pts, unsigned* keys, int cell, unsigned qrho, unsigned idx) {
-  unsigned* addr = keys + cell;
-  const unsigned key = (qrho << IDX_BITS32) | idx;
-  const unsigned old = atomicMin(addr, key);
-  if (old != KEY32_EMPTY && ((old ^ key) >> IDX_BITS32) == 0) settle32(frame_pts, addr, key, old);
+// candidate (point `idx`, coordinates v) against the holder of keys[cell]
+__device__ __forceinline__ void settle_candidate(const float4* __restrict__ frame_pts, unsigned* addr, const float4 v,
+                                                 unsigned idx) {
+  const double rho = rho_of_f4(v);
+  const unsigned my_key = (quant_rho(rho) << IDX_BITS32) | idx;
+  for (;;) {
+    const unsigned cur = *reinterpret_cast<volatile unsigned*>(addr);
+    if (cur == my_key) return;
+    if ((cur >> IDX_BITS32) < (my_key >> IDX_BITS32)) return;      // a nearer bucket holds the cell
+    const unsigned ci = cur & IDX_MASK32;
+    const double crho = rho_of_f4(__ldg(frame_pts + ci));
+    if (better(crho, ci, rho, idx)) return;
+    if (atomicCAS(addr, cur, my_key) == cur) return;
+  }
 }
 
 // quant_rho from the fp32 range rho32 = s*rsqrt(s) (relative error < 4e-7) when the result is
@@ -114,16 +114,42 @@ __device__ __forceinline__ bool tile_count(unsigned* tile, unsigned r) {
   if (ob >= 128u) atomicSub(tile + (r >> 2), 1u << sh);
   return ob >= 192u;
 }
-// Exact form: CAS loop that never lets a byte pass 128.
-__device__ __forceinline__ void tile_count_exact(unsigned* tile, unsigned r) {
+// The same in two steps, so that many counts can be in flight per thread.  issue: r = position
+// in the tile (>= T: not in this tile); returns (r | TC_VALID | previous byte << 24) or 0.
+// finish: the first arrival at a cell (previous byte 0) marks the cell's 32-byte sector in the
+// bitmap and, if the sector was not marked yet, appends it to the list of sectors to write;
+// an add on a byte that was already >= 128 is undone, and the >= 192 observation reported.
+constexpr unsigned TC_VALID = 1u << 23;
+__device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned r, unsigned T) {
+  if (r >= T) return 0u;
+  const unsigned sh = (r & 3u) * 8u;
+  const unsigned ob = (atomicAdd(tile + (r >> 2), 1u << sh) >> sh) & 0xFFu;
+  return r | TC_VALID | (ob << 24);
+}
+__device__ __forceinline__ void mark_sector(unsigned* bitmap, unsigned* list, unsigned* list_n, unsigned sct) {
+  const unsigned bit = 1u << (sct & 31u);
+  if (!(atomicOr(bitmap + (sct >> 5), bit) & bit)) list[atomicAdd(list_n, 1u)] = sct;
+}
+__device__ __forceinline__ bool tile_count_finish(unsigned* tile, unsigned* bitmap, unsigned* list, unsigned* list_n,
+                                                  unsigned packed) {
+  if (!(packed & TC_VALID)) return false;
+  const unsigned ob = packed >> 24, r = packed & (TC_VALID - 1u);
+  if (ob == 0u) { mark_sector(bitmap, list, list_n, r >> 3); return false; }
+  if (ob < 128u) return false;
+  atomicSub(tile + (r >> 2), 1u << ((r & 3u) * 8u));
+  return ob >= 192u;
+}
+// Exact form: CAS loop that never lets a byte pass 128.  Returns true for the first arrival.
+__device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
   const unsigned sh = (r & 3u) * 8u;
   unsigned* a = tile + (r >> 2);
   unsigned cur = *reinterpret_cast<volatile unsigned*>(a);
   while (((cur >> sh) & 0xFFu) < 128u) {
     const unsigned prev = atomicCAS(a, cur, cur + (1u << sh));
-    if (prev == cur) break;
+    if (prev == cur) return ((cur >> sh) & 0xFFu) == 0u;
     cur = prev;
   }
+  return false;
 }
 
 // ---- warp roles.  The last STORE_WARPS warps of the CTA do nothing but stream the zeros of
@@ -133,6 +159,8 @@ __device__ __forceinline__ void tile_count_exact(unsigned* tile, unsigned r) {
 constexpr int STORE_WARPS = 4;
 constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
 constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
+constexpr int MAX_BUCKETS = 16;                        // BEV entry buckets (consecutive tiles share one beyond 16 tiles)
+constexpr int NO_BUCKET = 31;
 constexpr unsigned FILL_PERIOD0 = 500000u;            // assumed frame period (SM cycles) until one is measured
 
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
@@ -154,15 +182,17 @@ __device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
 struct FusedArgs {
   const float4* pts;
   FrameSet fs;
-  unsigned* entries;   // [grid][per_cta] flat BEV output cell of every point (0xFFFFFFFF = none)
+  unsigned* entries;   // [grid][n_buckets][per_cta] BEV entries (output cell + head) by tile bucket
   unsigned* queue;     // [grid][per_cta] deferred point indices
+  uint2* cqueue;       // [grid][2*per_cta] collision records (cell, point index)
   long long per_cta;
   const double* lut64;
   float* range; int range_layout; int* winner;
   int range_vec4;      // H*W % 4 == 0 and 16-byte aligned range / winner buffers: vector resolve
   float* bev;
   int* status; int* dropped;
-  int tile_cells;      // BEV cells per shared-memory tile (multiple of 16)
+  int tile_log2;       // BEV cells per shared-memory tile = 1 << tile_log2 (>= 6)
+  int tiles_per_bucket, n_buckets;
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
   int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
 };
@@ -185,7 +215,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   float* const lut = reinterpret_cast<float*>(smem + main_words);
   // misc: [0] deferred count, [1] status bits, [2] dropped, [3] tile redo flag,
   //       [4] zero-fill progress: += 1 per store warp per finished frame, [5] frames begun by the compute warps,
-  //       [6] last frame period of the compute warps in SM cycles
+  //       [6] last frame period of the compute warps in SM cycles, [7] collision records
   unsigned* const misc = smem + main_words + 72;
   const int tid = threadIdx.x;
   const int hw = g.H * g.W;
@@ -242,8 +272,13 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   }
 
   // ======================================================================== compute warps
-  unsigned* const my_entries = a.entries + (size_t)blockIdx.x * a.per_cta;
+  unsigned* const my_buckets = a.entries + (size_t)blockIdx.x * a.n_buckets * a.per_cta;   // [bucket][per_cta]
+  unsigned* const bcnt = misc + 16;   // entries per bucket
+  const int lane = tid & 31;
+  const unsigned per_cta32 = (unsigned)a.per_cta;
+  const unsigned lane_lt = (1u << lane) - 1u;
   unsigned* const my_queue = a.queue + (size_t)blockIdx.x * a.per_cta;
+  uint2* const my_cq = a.cqueue + (size_t)blockIdx.x * a.per_cta * 2;   // up to 2 records per point
   const float height_bg = (float)g.height_bg;
   const unsigned cells_m1 = (unsigned)(cells - 1);
   const unsigned long long keep = l2_policy_evict_last();
@@ -256,12 +291,15 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     frame_span(a.fs, f, base, n);
     const float4* __restrict__ fp = a.pts + base;
     const long long E0 = (long long)f * cells, E1 = E0 + cells;
+    const unsigned head = (unsigned)(E0 & 7);   // tiles start on a 32-byte sector of the output
 
     // ---- S0
     if (g.enable_range)
       for (int i = tid; i < hw; i += CT) keys[i] = KEY32_EMPTY;
     if (tid < 4) misc[tid] = 0u;
+    if (tid >= 16 && tid < 16 + MAX_BUCKETS) misc[tid] = 0u;
     if (tid == 0) {
+      misc[7] = 0u; misc[8] = 0u; misc[9] = 0u;
       misc[5] = frames_done + 1;   // lets the zero-fill warps start on the next frame
       const long long now = clock64();
       if (frames_done) misc[6] = (unsigned)min(now - t_frame, 0x7FFFFFFFll);   // frame period for the fill pacing
@@ -284,34 +322,61 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const long long l = i0 + 2 * 4 * CT + (long long)tid * 8;
         if (tid < 4 * CT / 8 && l < n && !(a.debug & 64)) prefetch_l2(fp + l);
       }
+      int cell[4];        // range-scan cell of the point, -1 = none (tail, deferred, range scan off)
+      unsigned key[4];
+      unsigned be[4];     // BEV entry = flat output cell of the point + head (tile coordinates)
+      int bb[4];          // its bucket, NO_BUCKET = not in the BEV
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const long long i = i0 + u * CT + tid;
+        cell[u] = -1; key[u] = 0u; be[u] = 0u; bb[u] = NO_BUCKET;
         if (i >= n) continue;
         const float x = v[u].x, y = v[u].y, z = v[u].z;
-        if (g.enable_bev) {
+        if (do_bev) {
           int bx = bev_bin_f32(x, g.bev_inv_x_f, g.bev_c0_x_f, g.bev_eps_x_f, g.nbx);
           int by = bev_bin_f32(y, g.bev_inv_y_f, g.bev_c0_y_f, g.bev_eps_y_f, g.nby);
           if (bx == -2) bx = bev_bin_f64((double)x, g.bev_start, g.bev_delta_x, g.nex);
           if (by == -2) by = bev_bin_f64((double)y, g.bev_start, g.bev_delta_y, g.ney);
-          // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
-          const unsigned e = (bx >= 0 && by >= 0) ? cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) : 0xFFFFFFFFu;
-          if (!(a.debug & 16)) st_u32_hint(my_entries + i, e, keep);
+          if (bx >= 0 && by >= 0) {
+            // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
+            be[u] = cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) + head;
+            const int t = (int)(be[u] >> a.tile_log2);
+            bb[u] = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
+          }
         }
         if (g.enable_range) {
           const float s = fmaf(z, z, fmaf(y, y, x * x));
-          const float rs = rsqrtf(s);
+          const float rs = __frsqrt_rn(s);
           float xi, yi, q;
           range_coords_fast(g, x, y, z, rs, xi, yi, q);
           int row, col;
           if (range_cell_decide(g, xi, yi, q, row, col)) {
-            if (a.debug & 32) { if (row * g.W + col == -77) keys[0] = 0; } else
-            key_min32(fp, keys, row * g.W + col, quant_rho_guarded(v[u], s * rs), (unsigned)i);
+            cell[u] = row * g.W + col;
+            key[u] = (quant_rho_guarded(v[u], s * rs) << IDX_BITS32) | (unsigned)i;
           } else {
             my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
           }
         }
       }
+      // BEV entries are appended to the bucket of their tile, one shared-memory atomic per
+      // (warp, bucket): lanes with the same bucket elect a leader that reserves the slots
+      if (do_bev && !(a.debug & 16)) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const unsigned m = __match_any_sync(0xFFFFFFFFu, bb[u]);
+          const int leader = __ffs(m) - 1;
+          unsigned slot = 0u;
+          if (lane == leader && bb[u] != NO_BUCKET) slot = atomicAdd(&bcnt[bb[u]], (unsigned)__popc(m));
+          slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + (unsigned)__popc(m & lane_lt);
+          if (bb[u] != NO_BUCKET) st_u32_hint(my_buckets + ((unsigned)bb[u] * per_cta32 + slot), be[u], keep);
+        }
+      }
+      // the four shared-memory atomics go out back to back; their results are looked at afterwards
+      unsigned old[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !(a.debug & 32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) note_collision(my_cq, misc, cell[u], key[u], old[u]);
     }
     compute_sync();
     PROF_STAMP(1);
@@ -330,7 +395,34 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           atomicOr(&misc[1], (unsigned)err);
           atomicAdd(&misc[2], 1u);
         } else {
-          key_min32(fp, keys, row * g.W + col, quant_rho(rho), i);
+          const int cell = row * g.W + col;
+          const unsigned key = (quant_rho(rho) << IDX_BITS32) | i;
+          note_collision(my_cq, misc, cell, key, atomicMin(keys + cell, key));
+        }
+      }
+      compute_sync();
+      // ---- S1d: exact settlement of the recorded equal-bucket candidates, 4 per thread in flight
+      {
+        const unsigned cn = misc[7];
+        for (unsigned j0 = 0; j0 < cn; j0 += 4 * CT) {
+          uint2 en[4];
+          float4 pv[4];
+          bool act[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const unsigned j = j0 + u * CT + tid;
+            act[u] = j < cn;
+            if (act[u]) en[u] = my_cq[j];
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            // the current holder itself has nothing to do
+            if (act[u] && (keys[en[u].x] & IDX_MASK32) == en[u].y) act[u] = false;
+            if (act[u]) pv[u] = __ldg(fp + en[u].y);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (act[u]) settle_candidate(fp, keys + en[u].x, pv[u], en[u].y);
         }
       }
       compute_sync();
@@ -350,8 +442,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const int ntask = kmax * g.H;
 #pragma unroll 1
         for (int pass = (a.debug & 8) ? 1 : 0; pass < 2; ++pass) {
-          for (int t = tid; t < ntask; t += CT) {
-            const int k = t / g.H, r = t - k * g.H;
+          int k = tid / g.H, r = tid - k * g.H;          // task t = k * H + r, advanced without divisions
+          const int dk = CT / g.H, dr = CT - dk * g.H;
+          for (int t = tid; t < ntask; t += CT, k += dk, r += dr) {
+            if (r >= g.H) { r -= g.H; ++k; }
             const int gid = ((r * g.W + 3) >> 2) + k;
             if (gid >= (((r + 1) * g.W + 3) >> 2)) continue;
             const int c = gid << 2;
@@ -434,41 +528,54 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       if (a.dropped) a.dropped[f] = 0;
     }
 
-    // ---- S2: BEV, one flat tile of the output at a time.  Tiles start on a 32-byte sector.
+    // ---- S2: BEV, one flat tile of the output at a time.  Tiles are T = 2^tile_log2 cells and
+    // start on a 32-byte sector of the output (tile coordinates = frame cell + head).  Shared
+    // memory now holds: u8 counts of the tile | sector bitmap | list of non-empty sectors.
     if (do_bev) {
-      const int T = a.tile_cells, tw = T >> 2;
-      for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+      const int T = 1 << a.tile_log2, tw = T >> 2, bw = (T >> 8) > 0 ? (T >> 8) : 1;
+      unsigned* const bitmap = tile + tw;      // one bit per 8-cell sector of the tile
+      unsigned* const list = bitmap + bw;      // sectors that hold a non-empty cell (<= T/8)
+      for (int w = tid; w < tw + bw; w += CT) tile[w] = 0u;
       compute_sync();
-      const uint4* const entries4 = reinterpret_cast<const uint4*>(my_entries);
-      const long long n4 = (n + 3) >> 2;
-      for (long long B = E0 & ~7ll; B < E1; B += T) {
-        const long long lo = B > E0 ? B : E0, hi = B + T < E1 ? B + T : E1;
-        const unsigned elo = (unsigned)(lo - E0), ehi = (unsigned)(hi - E0);
-        const unsigned span = ehi - elo;
-        const int shift = (int)(E0 - B);
+      const long long B0 = E0 - head;          // global cell of tile coordinate 0
+      const unsigned span_all = (unsigned)cells + head;
+      const int n_tiles = (int)((span_all + (unsigned)T - 1u) >> a.tile_log2);
+      for (int t = 0; t < n_tiles; ++t) {
+        const unsigned tlo = (unsigned)t << a.tile_log2;                 // tile coordinates of this tile
+        const int bkt = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
+        const unsigned cnt = bcnt[bkt];
+        const uint4* const bucket4 = reinterpret_cast<const uint4*>(my_buckets + (size_t)bkt * a.per_cta);
+        const unsigned n4 = (cnt + 3u) >> 2;
+        unsigned* const list_n = misc + 8 + (t & 1);   // double buffered: the other one is reset meanwhile
         bool danger = false;
-        // the entry list of S1 (L2 resident), 16 bytes = 4 entries per load, ENTRY_BATCH loads in flight
-        for (long long q0 = 0; q0 < n4; q0 += (long long)ENTRY_BATCH * CT) {
+        for (unsigned q0 = 0; q0 < n4; q0 += ENTRY_BATCH * CT) {
           uint4 e[ENTRY_BATCH];
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            const long long q = q0 + u * CT + tid;
-            e[u] = q < n4 ? ld_u32x4_hint(entries4 + q, keep) : make_uint4(~0u, ~0u, ~0u, ~0u);
+            const unsigned q = q0 + u * CT + tid;
+            e[u] = q < n4 ? ld_u32x4_hint(bucket4 + q, keep) : make_uint4(~0u, ~0u, ~0u, ~0u);
+            if (4u * q + 4u > cnt) {   // last word of the bucket: slots past cnt hold stale entries
+              if (4u * q + 1u > cnt) e[u].x = ~0u;
+              if (4u * q + 2u > cnt) e[u].y = ~0u;
+              if (4u * q + 3u > cnt) e[u].z = ~0u;
+              e[u].w = ~0u;
+            }
           }
+          // stage 1: all counts go out back to back; every slot keeps (position | valid | old byte << 24)
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            const long long q = q0 + u * CT + tid;
-            if (4 * q + 4 > n) {   // last word of the list: slots past n hold stale entries
-              const long long m = n - 4 * q;
-              if (m < 2) e[u].y = ~0u;
-              if (m < 3) e[u].z = ~0u;
-              if (m < 4) e[u].w = ~0u;
-              if (m < 1) e[u].x = ~0u;
-            }
-            if (e[u].x - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].x + shift));
-            if (e[u].y - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].y + shift));
-            if (e[u].z - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].z + shift));
-            if (e[u].w - elo < span) danger |= tile_count(tile, (unsigned)((int)e[u].w + shift));
+            e[u].x = tile_count_issue(tile, e[u].x - tlo, (unsigned)T);
+            e[u].y = tile_count_issue(tile, e[u].y - tlo, (unsigned)T);
+            e[u].z = tile_count_issue(tile, e[u].z - tlo, (unsigned)T);
+            e[u].w = tile_count_issue(tile, e[u].w - tlo, (unsigned)T);
+          }
+          // stage 2: first arrival at a cell marks its sector; saturation fix-ups (rare)
+#pragma unroll
+          for (int u = 0; u < ENTRY_BATCH; ++u) {
+            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].x);
+            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].y);
+            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].z);
+            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].w);
           }
         }
         if (danger) misc[3] = 1u;
@@ -482,33 +589,37 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         PROF_STAMP(4);
         if (misc[3]) {  // a byte may have wrapped: redo this tile with the exact (CAS) form
           compute_sync();
-          if (tid == 0) misc[3] = 0u;
-          for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+          if (tid == 0) { misc[3] = 0u; *list_n = 0u; }
+          for (int w = tid; w < tw + bw; w += CT) tile[w] = 0u;
           compute_sync();
-          for (long long i = tid; i < n; i += CT) {
-            const unsigned e = __ldcg(my_entries + i);
-            if (e >= elo && e < ehi) tile_count_exact(tile, (unsigned)((int)e + shift));
+          const unsigned* const bucket = my_buckets + (size_t)bkt * a.per_cta;
+          for (unsigned i = tid; i < cnt; i += CT) {
+            const unsigned r = __ldcg(bucket + i) - tlo;
+            if (r < (unsigned)T && tile_count_exact(tile, r)) mark_sector(bitmap, list, list_n, r >> 3);
           }
           compute_sync();
           PROF_STAMP(5);
         }
-        // scan the tile two words (8 cells = one 32-byte sector) at a time; only sectors with a
-        // non-empty cell are written (over the zero fill), and their tile words re-zeroed
+        // write the non-empty sectors (8 cells = 32 bytes) over the zero fill; re-zero what was used
         {
-          const int rel_lo = (int)(lo - B), rel_hi = (int)(hi - B);
+          const unsigned ln = *list_n;
+          if (tid == 0) misc[8 + ((t + 1) & 1)] = 0u;
+          const long long B = B0 + tlo;                          // global cell of the tile's first cell
+          const int rel_lo = t == 0 ? (int)head : 0;             // cells of THIS frame inside the tile
+          const long long rem = (long long)span_all - tlo;
+          const int rel_hi = rem < T ? (int)rem : T;
           uint2* const tile2 = reinterpret_cast<uint2*>(tile);
           float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
-          const int np = (rel_hi + 7) >> 3;
-#pragma unroll 4
-          for (int p = tid; p < np; p += CT) {
-            const uint2 w = tile2[p];
-            if ((w.x | w.y) == 0u) continue;
-            tile2[p] = make_uint2(0u, 0u);
+          for (unsigned j = tid; j < ln; j += CT) {
+            const unsigned sct = list[j];
+            const uint2 w = tile2[sct];
+            tile2[sct] = make_uint2(0u, 0u);
+            bitmap[sct >> 5] = 0u;
             const float4 v0 = lut4(lut, w.x), v1 = lut4(lut, w.y);
-            const int c0 = p << 3;
+            const int c0 = (int)(sct << 3);
             if (c0 >= rel_lo && c0 + 8 <= rel_hi) {
-              __stcs(o4 + 2 * p, v0);
-              __stcs(o4 + 2 * p + 1, v1);
+              __stcs(o4 + 2 * sct, v0);
+              __stcs(o4 + 2 * sct + 1, v1);
             } else {  // frame head / tail: only the cells of THIS frame
               const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
@@ -526,6 +637,25 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
 // ---------------------------------------------------------------------------------------
 static int main_words_max() { return SMEM_LIMIT / 4 - SMEM_MISC_WORDS; }
+
+
+// S2 tile geometry: T = 2^p cells with T (u8 counts) + T/64 (sector bitmap) + T/2 (sector list)
+// bytes of shared memory; at most MAX_BUCKETS entry buckets, consecutive tiles share a bucket.
+FusedGeom fused_geometry(const DevGrid& g) {
+  FusedGeom o;
+  o.tile_log2 = 6; o.tiles_per_bucket = 1; o.n_buckets = 1; o.s2_words = 0;
+  if (!g.enable_bev) return o;
+  const long long cells = (long long)g.nbx * g.nby;
+  auto words = [](int p) { const long long T = 1ll << p; return (int)(T / 4 + (T / 256 > 0 ? T / 256 : 1) + T / 8); };
+  int p = 6;
+  while (p < 22 && (1ll << p) < cells + 8 && words(p + 1) <= main_words_max()) ++p;
+  o.tile_log2 = p;
+  o.s2_words = (words(p) + 3) & ~3;
+  const long long n_tiles = (cells + 7 + (1ll << p) - 1) >> p;
+  o.tiles_per_bucket = (int)((n_tiles + MAX_BUCKETS - 1) / MAX_BUCKETS);
+  o.n_buckets = (int)((n_tiles + o.tiles_per_bucket - 1) / o.tiles_per_bucket);
+  return o;
+}
 
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n) {
   const bool packed = src.dtype == 0 && src.stride == 16 && src.ox == 0 && src.oy == 4 && src.oz == 8 &&
@@ -552,25 +682,21 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
     attr_set = true;
   }
   const long long cells = (long long)g.nbx * g.nby;
-  int tile_words = 0;
-  if (g.enable_bev) {
-    long long need = ((cells + 7 + 3) / 4 + 3) & ~3ll;  // whole frame incl. an unaligned head (<= 7 cells)
-    const int cap = main_words_max() & ~3;
-    tile_words = (int)(need < cap ? need : cap);         // tile_cells multiple of 16
-    if (tile_words < 4) tile_words = 4;
-  }
+  int s2_words = 0;
+  FusedGeom geo = fused_geometry(g);
+  if (g.enable_bev) s2_words = geo.s2_words;
   int main_words = g.enable_range ? g.H * g.W : 0;
-  if (tile_words > main_words) main_words = tile_words;
+  if (s2_words > main_words) main_words = s2_words;
   main_words = (main_words + 3) & ~3;
   FusedArgs a;
   a.pts = reinterpret_cast<const float4*>(src.data);
   a.fs = fs;
-  a.entries = fx.entries; a.queue = fx.queue; a.per_cta = fx.per_cta;
+  a.entries = fx.entries; a.queue = fx.queue; a.cqueue = reinterpret_cast<uint2*>(fx.cqueue); a.per_cta = fx.per_cta;
   a.lut64 = s.lut;
   a.range = (float*)out.range; a.range_layout = out.range_layout; a.winner = out.range_winner;
   a.bev = (float*)out.bev;
   a.status = out.status; a.dropped = out.dropped;
-  a.tile_cells = tile_words * 4;
+  a.tile_log2 = geo.tile_log2; a.tiles_per_bucket = geo.tiles_per_bucket; a.n_buckets = geo.n_buckets;
   a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
   a.prof = fx.prof;
   a.debug = fx.debug;
@@ -592,7 +718,7 @@ __global__ void __launch_bounds__(256) k_selftest_fastpath(const __grid_constant
     const float4 v = __ldg(pts + i);
     const float x = v.x, y = v.y, z = v.z;
     const float s = fmaf(z, z, fmaf(y, y, x * x));
-    const float rs = rsqrtf(s);
+    const float rs = __frsqrt_rn(s);
     float xi, yi, q;
     range_coords_fast(g, x, y, z, rs, xi, yi, q);
     Pt p; p.x = x; p.y = y; p.z = z; p.it = v.w;

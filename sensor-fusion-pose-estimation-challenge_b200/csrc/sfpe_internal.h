@@ -59,11 +59,14 @@ cudaError_t launch_colormap(const void* img, int dtype, long long n, int cmap, i
 struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]
   unsigned* queue;     // [grid][per_cta]
+  unsigned* cqueue;    // [grid][4*per_cta] words: collision records
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
   long long* prof;     // optional [grid][8] phase cycle accumulators
   int debug;           // sfpe_params.reserved[0]: bit 0 = skip the BEV zero fill (timing experiments only)
 };
+struct FusedGeom { int tile_log2, tiles_per_bucket, n_buckets, s2_words; };
+FusedGeom fused_geometry(const DevGrid& g);
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n);
 int fused_grid(int device, int n_frames);
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
