@@ -32,6 +32,17 @@ def algorithmic_bytes(n_pts, nbx, nby, c_bev=1):
     return 16 * n_pts + 4 * 3 * H * W + 4 * c_bev * nbx * nby
 
 
+def measured_traffic(path_name, sweeps):
+    """dram__bytes_read+write per launch of the dominant kernel from the committed ncu capture
+    (profiles/traffic.json, bytes per sweep measured on a 296-sweep launch), scaled to this launch."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        t = json.load(open(p)).get(path_name)
+        return None if not t else float(t["dram_bytes_per_sweep"]) * sweeps
+    except (OSError, ValueError, KeyError):
+        return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(p):
@@ -106,43 +117,58 @@ def _cpu_worker(args):
     return time.perf_counter() - t0
 
 
-def cpu_reference_pass(n_sweeps, sensor, bev_res, cores, seed0=0):
-    """One bounded sample: n_sweeps sweeps spread over `cores` worker processes.  Returns seconds (wall)."""
-    import multiprocessing as mp
-    chunks = [list(range(seed0 + i, seed0 + n_sweeps, cores)) for i in range(cores)]
-    chunks = [c for c in chunks if c]
-    ctx = mp.get_context("spawn")
-    with ctx.Pool(len(chunks)) as pool:
-        pool.map(_cpu_worker, [([c[0]], sensor, bev_res) for c in chunks])     # warm the workers (imports)
+class CpuReference:
+    """The reference's numpy algorithm on all host cores: one persistent pool of worker processes
+    (spawn, each pinned to its own disjoint sweeps).  pass_(n) rasterises n sweeps, returns wall seconds."""
+
+    def __init__(self, sensor, bev_res, cores=None):
+        import multiprocessing as mp
+        self.cores = cores or os.cpu_count() or 1
+        self.sensor, self.bev_res = sensor, bev_res
+        self.pool = mp.get_context("spawn").Pool(self.cores)
+        self.pool.map(_cpu_worker, [([i], sensor, bev_res) for i in range(self.cores)])     # imports + warm-up
+
+    def pass_(self, n_sweeps, seed0=0):
+        chunks = [list(range(seed0 + i, seed0 + n_sweeps, self.cores)) for i in range(self.cores)]
+        chunks = [c for c in chunks if c]
         t0 = time.perf_counter()
-        pool.map(_cpu_worker, [(c, sensor, bev_res) for c in chunks])
+        self.pool.map(_cpu_worker, [(c, self.sensor, self.bev_res) for c in chunks])
         return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
 
 
 def run_reference(a):
     """--impl reference: the reference's own CPU algorithm (oracle port; the reference is Python and
-    cannot travel to the GPU box) on all host cores, same metric / config."""
+    cannot travel to the GPU box) on all host cores, same metric / config.  Each step is a bounded
+    sample of the workload (4 sweeps per core)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
-    per_step = max(cores, 8)
+    ref = CpuReference(a.sensor, (a.bev_res, a.bev_res))
+    cores = ref.cores
+    per_step = cores * 4
     times = []
     for i in range(a.warmup + a.steps):
-        dt = cpu_reference_pass(per_step, a.sensor, (a.bev_res, a.bev_res), cores, seed0=i * per_step)
+        dt = ref.pass_(per_step, seed0=i * per_step)
         if i >= a.warmup:
             times.append(dt)
+    ref.close()
     total = sum(times)
     val = per_step * len(times) / total
     cfg = workload_config(a)
     line = {
         "impl": "reference", "metric": "lidar sweeps/s (BEV+range projection)", "value": val, "unit": "sweeps/s",
+        "points_per_s": val * a.n_pts,
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": cfg,
         "cpu_baseline": {"value": val, "unit": "sweeps/s", "cores": cores, "kind": "port",
-                         "sample": "%d sweeps per step x %d steps, numpy port of the reference "
-                                   "(3x front view + histogram2d + per-cell python normalize loop)" % (per_step, len(times))},
+                         "sample": "%d sweeps per step x %d steps of the same workload, numpy port of the reference "
+                                   "(3x front view + histogram2d + per-cell python normalize loop) in %d processes"
+                                   % (per_step, len(times), cores)},
         "e2e": {"value": val, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -245,7 +271,7 @@ def run_ours(a):
             "data": "synthetic", "config": workload_config(a),
             "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": measured_traffic(pr.last_path, a.sweeps), "peak_source": peak_src,
                          "algorithmic_bytes_per_sweep": bytes_sweep, "launch_ms": med_ms,
                          "kernel": "fused k_fused_sweep (one launch per step)" if pr.last_path == "fused"
                          else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
@@ -256,12 +282,15 @@ def run_ours(a):
         if e2e is not None:
             line["e2e"] = e2e
         if not a.no_cpu and world == 1:
-            cores = os.cpu_count() or 1
-            n = max(cores, 8) * 2
-            dt = cpu_reference_pass(n, a.sensor, (a.bev_res, a.bev_res), cores)
-            line["cpu_baseline"] = {"value": n / dt, "unit": "sweeps/s", "cores": cores, "kind": "port",
+            ref = CpuReference(a.sensor, (a.bev_res, a.bev_res))
+            n = ref.cores * 8
+            dt = ref.pass_(n)
+            n = int(max(ref.cores * 8, min(4096, n * 15.0 / max(dt, 1e-3))))     # aim at ~15 s of wall time
+            dt = ref.pass_(n, seed0=1000)
+            ref.close()
+            line["cpu_baseline"] = {"value": n / dt, "unit": "sweeps/s", "cores": ref.cores, "kind": "port",
                                     "sample": "%d sweeps of the same workload, numpy port of the reference in %d "
-                                              "processes (%.1f s)" % (n, cores, dt)}
+                                              "processes (%.1f s)" % (n, ref.cores, dt)}
         print(json.dumps(line))
     pr.close()
     if world > 1:

@@ -15,10 +15,12 @@ _lib.load()  # fail loudly if the CUDA library is not built
 
 from .projector import LidarProjector  # noqa: E402
 from .host_batch import HostBatchPipeline  # noqa: E402
+from .streaming import StreamingFrontView  # noqa: E402
 from . import synth  # noqa: E402,F401
+from .sharding import shard_frames, shard_points  # noqa: E402,F401
 from .process import globals as grid_globals  # noqa: E402,F401
 from .process.extract_rosbag_lidar import generate_lidar_2d_front_view, lidar_2d_front_view  # noqa: E402,F401
 from .common.birds_eye_view_generator import birds_eye_view_density, generate_birds_eye_view  # noqa: E402,F401
 
-__all__ = ["LidarProjector", "HostBatchPipeline", "generate_lidar_2d_front_view", "lidar_2d_front_view",
-           "generate_birds_eye_view", "birds_eye_view_density", "synth", "grid_globals"]
+__all__ = ["LidarProjector", "HostBatchPipeline", "StreamingFrontView", "generate_lidar_2d_front_view", "lidar_2d_front_view",
+           "generate_birds_eye_view", "birds_eye_view_density", "synth", "grid_globals", "shard_frames", "shard_points"]

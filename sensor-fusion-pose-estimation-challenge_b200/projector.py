@@ -197,6 +197,25 @@ class LidarProjector:
         _lib.check(rc, self._ctx)
         return out
 
+    # ------------------------------------------------------------------ PointCloud2 blob -> packed points
+    def decode_pointcloud2(self, blob, n, point_step, offsets=(0, 4, 8, 16), dtype="f32", out=None, stream=None):
+        """blob: CUDA uint8 tensor holding a sensor_msgs/PointCloud2 `data` buffer (n points of
+        point_step bytes; x,y,z,intensity at `offsets`, FLOAT32 or FLOAT64).  Returns a CUDA
+        float32 (n,4) tensor -- what np.array(list(read_points(msg))) yields on the host in
+        team_sf_rosnode/scripts/lidar_predict.py:64-65, without the Python per-point loop."""
+        torch = _torch()
+        if not blob.is_cuda or blob.device.index != self.device or blob.numel() < n * point_step:
+            raise ValueError("blob must be a CUDA byte tensor of at least n*point_step bytes on cuda:%d" % self.device)
+        if out is None:
+            out = torch.empty((n, 4), dtype=torch.float32, device=blob.device)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        dt = _lib.SFPE_F32 if dtype == "f32" else _lib.SFPE_F64
+        rc = self.lib.sfpe_decode_pointcloud2(self._ctx, blob.data_ptr(), int(n), int(point_step), *[int(o) for o in offsets],
+                                              dt, out.data_ptr(), C.c_void_p(int(stream)))
+        _lib.check(rc, self._ctx)
+        return out
+
     # ------------------------------------------------------------------ one sweep, host in / host out
     def project_sweep_host(self, points, columns=(0, 1, 2, 3), range_dtype=np.float64, range_layout="chw",
                            bev_dtype=np.float64, want_range=True, want_bev=True, want_winner=False):

@@ -74,3 +74,20 @@ def as_reference_array(points_f32):
     out = np.zeros((n, 5), dtype=np.float64)
     out[:, :4] = points_f32
     return out
+
+
+# Velodyne driver PointCloud2 layout: point_step 32 bytes,
+# x,y,z float32 @0/4/8, intensity float32 @16, ring uint16 @20.
+PC2_POINT_STEP = 32
+PC2_OFFSETS = (0, 4, 8, 16)
+
+
+def make_pointcloud2_blob(points_f32, beams=32):
+    """uint8 array (N*32,) laid out like the `data` field of a /velodyne_points message."""
+    n = len(points_f32)
+    rec = np.zeros(n, dtype=np.dtype({"names": ["x", "y", "z", "intensity", "ring"],
+                                      "formats": ["<f4", "<f4", "<f4", "<f4", "<u2"],
+                                      "offsets": [0, 4, 8, 16, 20], "itemsize": PC2_POINT_STEP}))
+    rec["x"], rec["y"], rec["z"], rec["intensity"] = points_f32[:, 0], points_f32[:, 1], points_f32[:, 2], points_f32[:, 3]
+    rec["ring"] = np.arange(n) % beams
+    return rec.view(np.uint8).reshape(-1)

@@ -320,3 +320,38 @@ def test_fused_path_adversarial_boundaries(pkg):
     assert res["_path"] == "fused"
     for f, s in enumerate(sweeps):
         _check_frame(res, f, s)
+
+
+# ---------------------------------------------------------------- next rows: PointCloud2 decode, streaming entry
+def test_decode_pointcloud2_matches_struct_unpack(pkg, synth):
+    import torch
+    pts = synth.make_sweep("hdl32", seed=90, n_az=500)
+    blob = synth.make_pointcloud2_blob(pts)
+    pr = pkg.LidarProjector(device=0)
+    got = pr.decode_pointcloud2(torch.from_numpy(blob).cuda(), len(pts), synth.PC2_POINT_STEP, synth.PC2_OFFSETS)
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), pts)
+    # float64 fields (datatype 8) are rounded to float32 like np.float32(value)
+    rec = np.zeros(len(pts), dtype=np.dtype({"names": list("xyzi"), "formats": ["<f8"] * 4, "offsets": [0, 8, 16, 24], "itemsize": 40}))
+    for k, c in zip("xyzi", range(4)):
+        rec[k] = pts[:, c].astype(np.float64) * (1 + 1e-9)
+    got64 = pr.decode_pointcloud2(torch.from_numpy(rec.view(np.uint8).reshape(-1)).cuda(), len(pts), 40, (0, 8, 16, 24), dtype="f64")
+    torch.cuda.synchronize()
+    want = np.stack([rec[k] for k in "xyzi"], axis=1).astype(np.float32)
+    assert np.array_equal(got64.cpu().numpy(), want)
+    pr.close()
+
+
+def test_streaming_entry_matches_oracle(pkg, synth):
+    sv = pkg.StreamingFrontView(device=0, max_points=70000)
+    for seed in (91, 92):
+        pts = synth.make_sweep("hdl32", seed=seed, dropout=0.02)
+        out = sv(synth.make_pointcloud2_blob(pts).tobytes())
+        o = lo.front_view(_P(pts))
+        assert out.shape == (32, 1801, 3) and out.dtype == np.float32
+        for c, k in enumerate(("distance", "height", "intensity")):          # train/predict.py:339-341 order
+            assert np.array_equal(out[..., c], o[k].astype(np.float32)), k
+    bad = np.vstack([synth.make_sweep("hdl32", seed=93, n_az=8), np.zeros((1, 4), np.float32)])
+    with pytest.raises(IndexError):
+        sv(synth.make_pointcloud2_blob(bad).tobytes())
+    sv.close()
