@@ -257,6 +257,7 @@ def run_ours(a):
         phases["sm_cycles_per_sweep"] = tot / (2 * a.sweeps)
 
     status_bad = int((out["status"] != 0).sum().item())
+    dropped_mean = float(out["dropped"].float().mean().item()) if "dropped" in out else None
     if rank == 0:
         peak, peak_src = measured_peak()
         bytes_sweep = algorithmic_bytes(a.n_pts, pr.nbx, pr.nby)
@@ -269,7 +270,7 @@ def run_ours(a):
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": total_ms / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": workload_config(a),
-            "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad,
+            "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad, "dropped_mean": dropped_mean,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(pr.last_path, a.sweeps), "peak_source": peak_src,
                          "algorithmic_bytes_per_sweep": bytes_sweep, "launch_ms": med_ms,

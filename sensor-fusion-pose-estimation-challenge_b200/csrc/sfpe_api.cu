@@ -289,7 +289,7 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.per_cta = (max_n + 255) & ~255ll;
     if (fx.per_cta < 256) fx.per_cta = 256;
     const FusedGeom geo = fused_geometry(g);
-    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 4);   // entry buckets + deferred queue + collision records
+    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 12);   // entry buckets + deferred queue + collision records (two levels)
     const int grc = grow(c, &c->fused_buf, &c->fused_cap, need);
     if (grc) return grc;
     fx.entries = (unsigned*)c->fused_buf;

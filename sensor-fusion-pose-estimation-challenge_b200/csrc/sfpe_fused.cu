@@ -24,13 +24,13 @@
 
 namespace sfpe {
 
-constexpr int FUSED_THREADS = 640;
+constexpr int FUSED_THREADS = 512;
 constexpr int IDX_BITS32 = 18;                       // point index bits of the 32-bit key
 constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
 constexpr int SMEM_MISC_WORDS = 128;                 // LUT (65 floats) + counters
-constexpr int ENTRY_BATCH = 2;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
+constexpr int ENTRY_BATCH = 3;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
 // ---- L2 residency hints: the entry list is written once and read once per BEV tile
@@ -63,33 +63,40 @@ __device__ __forceinline__ double rho_of_f4(const float4 v) {
 }
 
 // Winner keys whose quantised range is equal are settled exactly, but not where they are found:
-// a point that meets an equal-prefix key at its atomicMin only records the two candidates (itself
-// and the previous holder) in a per-CTA collision list; after the point pass every recorded
-// candidate tries to install itself over the current holder under the exact order (rho fp64,
-// index).  The best candidate of the winning bucket ends up in the key whatever the schedule:
-// it replaces any worse holder (CAS, retried) and no worse candidate can replace it.  Every
-// point of a bucket that holds more than one point is recorded (the first one by the second).
+// a point that meets an equal-bucket key at its atomicMin records itself in a per-CTA collision
+// list -- and the previous holder too if it has just displaced it (lower index), because a
+// displaced point is in nobody's list yet.  So every point of a bucket that holds more than one
+// point of a cell is either the holder of the key or recorded.  After the point pass every
+// recorded candidate tries to install itself over the current holder under the exact order
+// (rho fp64, index) with a CAS loop: the best candidate of the winning bucket ends up in the key
+// whatever the schedule -- it replaces any worse holder and no worse candidate can replace it.
 __device__ __forceinline__ void note_collision(uint2* __restrict__ cq, unsigned* misc, int cell, unsigned key, unsigned old) {
   if (old != KEY32_EMPTY && ((old ^ key) >> IDX_BITS32) == 0) {
-    const unsigned pos = atomicAdd(&misc[7], 2u);
+    const bool displaced = key < old;
+    const unsigned pos = atomicAdd(&misc[7], displaced ? 2u : 1u);
     cq[pos] = make_uint2((unsigned)cell, key & IDX_MASK32);
-    cq[pos + 1] = make_uint2((unsigned)cell, old & IDX_MASK32);
+    if (displaced) cq[pos + 1] = make_uint2((unsigned)cell, old & IDX_MASK32);
   }
 }
 
-// candidate (point `idx`, coordinates v) against the holder of keys[cell]
+// candidate (point idx, coordinates v) against the holder of *addr: `cur` is the key read
+// before and hv the coordinates of ITS point (both loaded by the caller, so that the loads of
+// several candidates are in flight together); reloaded only when the holder changes under us.
 __device__ __forceinline__ void settle_candidate(const float4* __restrict__ frame_pts, unsigned* addr, const float4 v,
-                                                 unsigned idx) {
+                                                 unsigned idx, unsigned cur, float4 hv) {
   const double rho = rho_of_f4(v);
   const unsigned my_key = (quant_rho(rho) << IDX_BITS32) | idx;
   for (;;) {
-    const unsigned cur = *reinterpret_cast<volatile unsigned*>(addr);
     if (cur == my_key) return;
     if ((cur >> IDX_BITS32) < (my_key >> IDX_BITS32)) return;      // a nearer bucket holds the cell
-    const unsigned ci = cur & IDX_MASK32;
-    const double crho = rho_of_f4(__ldg(frame_pts + ci));
-    if (better(crho, ci, rho, idx)) return;
-    if (atomicCAS(addr, cur, my_key) == cur) return;
+    if ((cur >> IDX_BITS32) == (my_key >> IDX_BITS32)) {
+      const unsigned ci = cur & IDX_MASK32;
+      if (better(rho_of_f4(hv), ci, rho, idx)) return;
+    }
+    const unsigned seen = atomicCAS(addr, cur, my_key);
+    if (seen == cur) return;
+    cur = seen;
+    hv = __ldg(frame_pts + (cur & IDX_MASK32));
   }
 }
 
@@ -156,7 +163,7 @@ __device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
 // the CTA's BEV frames (the per-SM store path, 32 B/clk, is the longest single resource of a
 // sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
 // the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
-constexpr int STORE_WARPS = 4;
+constexpr int STORE_WARPS = 2;
 constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
 constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
 constexpr int MAX_BUCKETS = 16;                        // BEV entry buckets (consecutive tiles share one beyond 16 tiles)
@@ -184,7 +191,7 @@ struct FusedArgs {
   FrameSet fs;
   unsigned* entries;   // [grid][n_buckets][per_cta] BEV entries (output cell + head) by tile bucket
   unsigned* queue;     // [grid][per_cta] deferred point indices
-  uint2* cqueue;       // [grid][2*per_cta] collision records (cell, point index)
+  uint2* cqueue;       // [grid][6*per_cta] collision records (cell | bucket << 16, point index)
   long long per_cta;
   const double* lut64;
   float* range; int range_layout; int* winner;
@@ -237,7 +244,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       // at most one frame ahead of the compute warps: the fill of frame k runs next to the
       // rasterisation of frame k-1 (an unbounded run-ahead would saturate HBM with zeros first
       // and starve the point pass of every SM)
-      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(500);
+      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(5000);
       // this frame's BEV is cells [E0, E1) of a.bev: full 16-byte words [W0, W1) + head / tail cells
       const long long E0 = (long long)f * cells, E1 = E0 + cells;
       const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
@@ -261,7 +268,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 #pragma unroll
         for (int u = 0; u < 8; ++u) __stcs(p + u * ST, z);
         t_next += interval;
-        while (clock64() < t_next) __nanosleep(64);
+        if (a.debug & 2048) { while (clock64() < t_next) __nanosleep(64); }
+        else for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
       }
       for (; left > 0; left -= ST, p += ST) __stcs(p, z);
       __threadfence_block();
@@ -278,7 +286,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const unsigned per_cta32 = (unsigned)a.per_cta;
   const unsigned lane_lt = (1u << lane) - 1u;
   unsigned* const my_queue = a.queue + (size_t)blockIdx.x * a.per_cta;
-  uint2* const my_cq = a.cqueue + (size_t)blockIdx.x * a.per_cta * 2;   // up to 2 records per point
+  uint2* const my_cq = a.cqueue + (size_t)blockIdx.x * a.per_cta * 6;   // <= 2n first-level records + <= 2 per live record (S1d)
   const float height_bg = (float)g.height_bg;
   const unsigned cells_m1 = (unsigned)(cells - 1);
   const unsigned long long keep = l2_policy_evict_last();
@@ -306,20 +314,27 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       t_frame = now;
     }
     // the first two S1 iterations of points are pulled into L2 while the keys are initialised
-    for (long long l = tid; l * 8 < n && l < 2 * (4 * CT / 8); l += CT) prefetch_l2(fp + l * 8);
+    for (long long l = tid; l * 8 < n && l < 3 * (4 * CT / 8); l += CT) prefetch_l2(fp + l * 8);
     compute_sync();
     PROF_STAMP(0);
 
     // ---- S1: one pass over the points
+    float4 nv4[4];   // points of the next iteration, loaded while the current one is rasterised
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = (long long)u * CT + tid;
+      if (i < n) nv4[u] = __ldg(fp + i);
+    }
     for (long long i0 = 0; i0 < n; i0 += 4 * CT) {
       float4 v[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const long long i = i0 + u * CT + tid;
-        if (i < n) v[u] = __ldg(fp + i);
+        v[u] = nv4[u];
+        const long long i = i0 + 4 * CT + u * CT + tid;
+        if (i < n) nv4[u] = __ldg(fp + i);
       }
       {  // L2 prefetch two iterations ahead (one 128-byte line = 8 points per thread)
-        const long long l = i0 + 2 * 4 * CT + (long long)tid * 8;
+        const long long l = i0 + 3 * 4 * CT + (long long)tid * 8;
         if (tid < 4 * CT / 8 && l < n && !(a.debug & 64)) prefetch_l2(fp + l);
       }
       int cell[4];        // range-scan cell of the point, -1 = none (tail, deferred, range scan off)
@@ -401,12 +416,15 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         }
       }
       compute_sync();
+      PROF_STAMP(2);
       // ---- S1d: exact settlement of the recorded equal-bucket candidates, 4 per thread in flight
+      // (record -> key from shared memory -> candidate and holder points together -> CAS)
       {
         const unsigned cn = misc[7];
         for (unsigned j0 = 0; j0 < cn; j0 += 4 * CT) {
           uint2 en[4];
-          float4 pv[4];
+          float4 pv[4], hv[4];
+          unsigned cur[4];
           bool act[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
@@ -416,20 +434,29 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            // the current holder itself has nothing to do
-            if (act[u] && (keys[en[u].x] & IDX_MASK32) == en[u].y) act[u] = false;
-            if (act[u]) pv[u] = __ldg(fp + en[u].y);
+            if (!act[u]) continue;
+            cur[u] = keys[en[u].x];
+            if ((cur[u] & IDX_MASK32) == en[u].y) { act[u] = false; continue; }   // the holder itself has nothing to do
+            if (a.debug & 512) { pv[u] = make_float4(1.f, 2.f, 3.f, (float)en[u].y); hv[u] = make_float4(1.f, 2.f, 3.f, (float)cur[u]); continue; }
+            pv[u] = __ldg(fp + en[u].y);
+            hv[u] = __ldg(fp + (cur[u] & IDX_MASK32));
+          }
+          if (a.debug & 256) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (act[u] && pv[u].x + hv[u].y == 1.2345f) keys[0] = 0u;
+            continue;
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u)
-            if (act[u]) settle_candidate(fp, keys + en[u].x, pv[u], en[u].y);
+            if (act[u]) settle_candidate(fp, keys + en[u].x, pv[u], en[u].y, cur[u], hv[u]);
         }
       }
       compute_sync();
-      PROF_STAMP(2);
+      PROF_STAMP(7);
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
-        if (a.dropped) a.dropped[f] = (int)misc[2];
+        if (a.dropped) a.dropped[f] = (a.debug & 128) ? (int)misc[7] : (int)misc[2];
       }
 
       // ---- S1c: resolve the range scan; output row r shows pre-flip row H-1-r   (:74)
@@ -437,64 +464,106 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         // Task (k, r) = k-th aligned group of 4 flat output cells whose first cell lies in output
         // row r; tasks run k-major / r-minor, so a warp (H = 32: one lane per row) gathers the
         // winners of ~4 neighbouring columns -- neighbouring points of a firing-order sweep.
-        // Pass A only prefetches every winner into L2 (no register, nothing waits); pass B gathers.
+        // One software-pipelined loop: the winners of task i+PF are prefetched into L2, those of
+        // task i+1 are gathered into registers, and task i is computed and stored meanwhile.
         const int kmax = ((g.W + 3) >> 2) + 1;
         const int ntask = kmax * g.H;
+        const int hs = (g.H & (g.H - 1)) == 0 ? __ffs(g.H) - 1 : -1;
+        constexpr int PF = 3;
+        // first cell of task t (a multiple of 4), or -1 when t is past the end / an empty slot
+        auto task_cell = [&](int t, int& r) -> int {
+          r = 0;
+          if (t >= ntask) return -1;
+          const int k = hs >= 0 ? t >> hs : t / g.H;
+          r = t - k * g.H;
+          const int gid = ((r * g.W + 3) >> 2) + k;
+          return gid >= (((r + 1) * g.W + 3) >> 2) ? -1 : gid << 2;
+        };
+        auto load_keys = [&](int c, int r, unsigned (&key)[4]) {
+          int orow = r, col = c - r * g.W;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            key[j] = keys[(g.H - 1 - orow) * g.W + col];
+            if (++col == g.W) { col = 0; ++orow; }
+          }
+        };
+        if (!(a.debug & 8)) {
 #pragma unroll 1
-        for (int pass = (a.debug & 8) ? 1 : 0; pass < 2; ++pass) {
-          int k = tid / g.H, r = tid - k * g.H;          // task t = k * H + r, advanced without divisions
-          const int dk = CT / g.H, dr = CT - dk * g.H;
-          for (int t = tid; t < ntask; t += CT, k += dk, r += dr) {
-            if (r >= g.H) { r -= g.H; ++k; }
-            const int gid = ((r * g.W + 3) >> 2) + k;
-            if (gid >= (((r + 1) * g.W + 3) >> 2)) continue;
-            const int c = gid << 2;
-            int orow = r, col = c - r * g.W;
+          for (int s = 1; s < PF; ++s) {   // prologue of the prefetch stream
+            int r;
+            const int c = task_cell(tid + s * CT, r);
+            if (c < 0) continue;
             unsigned key[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              key[j] = keys[(g.H - 1 - orow) * g.W + col];
-              if (++col == g.W) { col = 0; ++orow; }
-            }
-            if (pass == 0) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j)
-                if (key[j] != KEY32_EMPTY) prefetch_l2(fp + (key[j] & IDX_MASK32));
-              continue;
-            }
-            float4 v[4];
+            load_keys(c, r, key);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              if (key[j] != KEY32_EMPTY) v[j] = (a.debug & 4) ? make_float4(1.f, 2.f, 3.f, (float)key[j]) : __ldg(fp + (key[j] & IDX_MASK32));
-            float d[4], h[4], it[4];
-            int win[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
-              if (key[j] != KEY32_EMPTY) {
-                win[j] = (int)(key[j] & IDX_MASK32);
-                const double x = v[j].x, y = v[j].y;
-                d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
-                h[j] = v[j].z; it[j] = v[j].w;
-              }
-            }
-            if (a.debug & 2) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
-            if (a.range) {
-              if (a.range_layout == 0) {
-                float* o = a.range + (size_t)f * 3 * hw + c;
-                __stcs(reinterpret_cast<float4*>(o), make_float4(d[0], d[1], d[2], d[3]));
-                __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
-                __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
-              } else {
-                float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
-                __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
-                __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
-                __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
-              }
-            }
-            if (a.winner)
-              __stcs(reinterpret_cast<int4*>(a.winner + (size_t)f * hw + c), make_int4(win[0], win[1], win[2], win[3]));
+              if (key[j] != KEY32_EMPTY) prefetch_l2(fp + (key[j] & IDX_MASK32));
           }
+        }
+        unsigned nkey[4];
+        float4 nv[4];
+        int nr;
+        int nc = task_cell(tid, nr);
+        if (nc >= 0) {
+          load_keys(nc, nr, nkey);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (nkey[j] != KEY32_EMPTY) nv[j] = __ldg(fp + (nkey[j] & IDX_MASK32));
+        }
+#pragma unroll 1
+        for (int t = tid; t < ntask; t += CT) {
+          const int c = nc;
+          unsigned key[4];
+          float4 v[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { key[j] = nkey[j]; v[j] = nv[j]; }
+          if (!(a.debug & 8)) {
+            int pr;
+            const int pc = task_cell(t + PF * CT, pr);
+            if (pc >= 0) {
+              unsigned pk[4];
+              load_keys(pc, pr, pk);
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                if (pk[j] != KEY32_EMPTY) prefetch_l2(fp + (pk[j] & IDX_MASK32));
+            }
+          }
+          nc = task_cell(t + CT, nr);
+          if (nc >= 0) {
+            load_keys(nc, nr, nkey);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              if (nkey[j] != KEY32_EMPTY) nv[j] = (a.debug & 4) ? make_float4(1.f, 2.f, 3.f, (float)nkey[j]) : __ldg(fp + (nkey[j] & IDX_MASK32));
+          }
+          if (c < 0) continue;
+          float d[4], h[4], it[4];
+          int win[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
+            if (key[j] != KEY32_EMPTY) {
+              win[j] = (int)(key[j] & IDX_MASK32);
+              const double x = v[j].x, y = v[j].y;
+              d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
+              h[j] = v[j].z; it[j] = v[j].w;
+            }
+          }
+          if (a.debug & 2) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
+          if (a.range) {
+            if (a.range_layout == 0) {
+              float* o = a.range + (size_t)f * 3 * hw + c;
+              __stcs(reinterpret_cast<float4*>(o), make_float4(d[0], d[1], d[2], d[3]));
+              __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
+              __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
+            } else {
+              float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
+              __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
+              __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
+              __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
+            }
+          }
+          if (a.winner)
+            __stcs(reinterpret_cast<int4*>(a.winner + (size_t)f * hw + c), make_int4(win[0], win[1], win[2], win[3]));
         }
       } else {
         for (int c = tid; c < hw; c += CT) {
@@ -540,26 +609,41 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       const long long B0 = E0 - head;          // global cell of tile coordinate 0
       const unsigned span_all = (unsigned)cells + head;
       const int n_tiles = (int)((span_all + (unsigned)T - 1u) >> a.tile_log2);
+      // entries of a tile's bucket, ENTRY_BATCH 16-byte loads per thread; slots past the end of
+      // the bucket (stale) read as "not in this tile"
+      auto load_batch = [&](int t, unsigned q0, uint4 (&e)[ENTRY_BATCH]) {
+        const int bkt = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
+        const unsigned cnt = bcnt[bkt];
+        const uint4* const bucket4 = reinterpret_cast<const uint4*>(my_buckets + (size_t)bkt * a.per_cta);
+        const unsigned n4 = (cnt + 3u) >> 2;
+#pragma unroll
+        for (int u = 0; u < ENTRY_BATCH; ++u) {
+          const unsigned q = q0 + u * CT + tid;
+          e[u] = q < n4 ? ld_u32x4_hint(bucket4 + q, keep) : make_uint4(~0u, ~0u, ~0u, ~0u);
+          if (4u * q + 4u > cnt) {   // last word of the bucket
+            if (4u * q + 1u > cnt) e[u].x = ~0u;
+            if (4u * q + 2u > cnt) e[u].y = ~0u;
+            if (4u * q + 3u > cnt) e[u].z = ~0u;
+            e[u].w = ~0u;
+          }
+        }
+      };
+      uint4 pe[ENTRY_BATCH];   // first batch of the next tile, loaded while the current tile is written out
+      load_batch(0, 0u, pe);
       for (int t = 0; t < n_tiles; ++t) {
         const unsigned tlo = (unsigned)t << a.tile_log2;                 // tile coordinates of this tile
         const int bkt = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
         const unsigned cnt = bcnt[bkt];
-        const uint4* const bucket4 = reinterpret_cast<const uint4*>(my_buckets + (size_t)bkt * a.per_cta);
         const unsigned n4 = (cnt + 3u) >> 2;
         unsigned* const list_n = misc + 8 + (t & 1);   // double buffered: the other one is reset meanwhile
         bool danger = false;
         for (unsigned q0 = 0; q0 < n4; q0 += ENTRY_BATCH * CT) {
           uint4 e[ENTRY_BATCH];
+          if (q0 == 0) {
 #pragma unroll
-          for (int u = 0; u < ENTRY_BATCH; ++u) {
-            const unsigned q = q0 + u * CT + tid;
-            e[u] = q < n4 ? ld_u32x4_hint(bucket4 + q, keep) : make_uint4(~0u, ~0u, ~0u, ~0u);
-            if (4u * q + 4u > cnt) {   // last word of the bucket: slots past cnt hold stale entries
-              if (4u * q + 1u > cnt) e[u].x = ~0u;
-              if (4u * q + 2u > cnt) e[u].y = ~0u;
-              if (4u * q + 3u > cnt) e[u].z = ~0u;
-              e[u].w = ~0u;
-            }
+            for (int u = 0; u < ENTRY_BATCH; ++u) e[u] = pe[u];
+          } else {
+            load_batch(t, q0, e);
           }
           // stage 1: all counts go out back to back; every slot keeps (position | valid | old byte << 24)
 #pragma unroll
@@ -579,6 +663,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           }
         }
         if (danger) misc[3] = 1u;
+        if (t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
         // the zeros of this frame must have been issued before its non-empty sectors go out
         if (tid == 0) {
           const unsigned want = (unsigned)STORE_WARPS * (frames_done + 1);

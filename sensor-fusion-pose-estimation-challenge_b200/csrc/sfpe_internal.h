@@ -59,7 +59,7 @@ cudaError_t launch_colormap(const void* img, int dtype, long long n, int cmap, i
 struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]
   unsigned* queue;     // [grid][per_cta]
-  unsigned* cqueue;    // [grid][4*per_cta] words: collision records
+  unsigned* cqueue;    // [grid][12*per_cta] words: collision records
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
   long long* prof;     // optional [grid][8] phase cycle accumulators

@@ -6,5 +6,5 @@ mkdir -p gpurun_out
 for d in $1; do
   python bench.py --steps 4 --warmup 3 --no-e2e --no-cpu --phases --debug-flags $d > gpurun_out/dbg_$d.json 2>/dev/null
   python -c "
-import json; d=json.load(open('gpurun_out/dbg_$d.json')); p=d['phase_share']; t=p.pop('sm_cycles_per_sweep'); print('flags %3d  %7.0f sweeps/s  total %7.0f  '%($d,d['value'],t)+'  '.join('%s %6.0f'%(k[:9],v*t) for k,v in p.items()))"
+import json; d=json.load(open('gpurun_out/dbg_$d.json')); p=d['phase_share']; t=p.pop('sm_cycles_per_sweep'); print('flags %3d  %7.0f sweeps/s  drop %s total %7.0f  '%($d,d['value'],d.get('dropped_mean'),t)+'  '.join('%s %6.0f'%(k[:9],v*t) for k,v in p.items()))"
 done
