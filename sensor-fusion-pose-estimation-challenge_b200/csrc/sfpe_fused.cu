@@ -290,6 +290,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const float height_bg = (float)g.height_bg;
   const unsigned cells_m1 = (unsigned)(cells - 1);
   const unsigned long long keep = l2_policy_evict_last();
+  const int bucket_shift = a.tile_log2 + 31 - __clz(a.tiles_per_bucket);   // tiles_per_bucket is a power of two
   long long t_prev = clock64();
   unsigned frames_done = 0;
   long long t_frame = 0;
@@ -323,7 +324,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const long long i = (long long)u * CT + tid;
-      if (i < n) nv4[u] = __ldg(fp + i);
+      nv4[u] = i < n ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (long long i0 = 0; i0 < n; i0 += 4 * CT) {
       float4 v[4];
@@ -331,48 +332,68 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       for (int u = 0; u < 4; ++u) {
         v[u] = nv4[u];
         const long long i = i0 + 4 * CT + u * CT + tid;
-        if (i < n) nv4[u] = __ldg(fp + i);
+        nv4[u] = i < n ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       {  // L2 prefetch two iterations ahead (one 128-byte line = 8 points per thread)
         const long long l = i0 + 3 * 4 * CT + (long long)tid * 8;
         if (tid < 4 * CT / 8 && l < n && !(a.debug & 64)) prefetch_l2(fp + l);
       }
+      // Per point, branch-free (so that the four points of a thread interleave): every decision
+      // -- range-scan cell, range bucket, BEV bins -- is made in fp32 and PROVEN by its guard
+      // band; a point with any unproven decision is deferred as a whole to S1b (fp64).
       int cell[4];        // range-scan cell of the point, -1 = none (tail, deferred, range scan off)
       unsigned key[4];
       unsigned be[4];     // BEV entry = flat output cell of the point + head (tile coordinates)
       int bb[4];          // its bucket, NO_BUCKET = not in the BEV
+      bool defer[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const long long i = i0 + u * CT + tid;
-        cell[u] = -1; key[u] = 0u; be[u] = 0u; bb[u] = NO_BUCKET;
-        if (i >= n) continue;
+        const bool valid = i < n;
         const float x = v[u].x, y = v[u].y, z = v[u].z;
-        if (do_bev) {
-          int bx = bev_bin_f32(x, g.bev_inv_x_f, g.bev_c0_x_f, g.bev_eps_x_f, g.nbx);
-          int by = bev_bin_f32(y, g.bev_inv_y_f, g.bev_c0_y_f, g.bev_eps_y_f, g.nby);
-          if (bx == -2) bx = bev_bin_f64((double)x, g.bev_start, g.bev_delta_x, g.nex);
-          if (by == -2) by = bev_bin_f64((double)y, g.bev_start, g.bev_delta_y, g.ney);
-          if (bx >= 0 && by >= 0) {
-            // both axes reversed == flat index reversed   (birds_eye_view_generator.py:46)
-            be[u] = cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) + head;
-            const int t = (int)(be[u] >> a.tile_log2);
-            bb[u] = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
-          }
+        bool undecided = false;
+        be[u] = 0u; bb[u] = NO_BUCKET; cell[u] = -1; key[u] = 0u;
+        if (do_bev) {   // uniform
+          const float tx = fmaf(x, g.bev_inv_x_f, g.bev_c0_x_f), ty = fmaf(y, g.bev_inv_y_f, g.bev_c0_y_f);
+          const float flx = floorf(tx), fly = floorf(ty);
+          const float frx = tx - flx, fry = ty - fly;
+          const float nbxf = (float)g.nbx, nbyf = (float)g.nby;
+          const bool inx = frx > g.bev_eps_x_f && frx < 1.0f - g.bev_eps_x_f && tx > 0.0f && tx < nbxf;   // proven bin
+          const bool iny = fry > g.bev_eps_y_f && fry < 1.0f - g.bev_eps_y_f && ty > 0.0f && ty < nbyf;
+          const bool outx = tx < -1.0f || tx > nbxf + 1.0f;                                               // proven outside
+          const bool outy = ty < -1.0f || ty > nbyf + 1.0f;
+          // NaN: neither in nor out -> undecided -> fp64 (which drops it, like histogram2d)
+          undecided = !(outx || outy) && !(inx && iny);
+          const unsigned e = cells_m1 - ((unsigned)(int)flx * (unsigned)g.nby + (unsigned)(int)fly) + head;
+          const int bk = (int)(e >> bucket_shift);
+          const bool inside = valid && inx && iny;
+          be[u] = e;
+          bb[u] = inside ? bk : NO_BUCKET;
         }
-        if (g.enable_range) {
+        bool okr = true;
+        if (g.enable_range) {   // uniform
           const float s = fmaf(z, z, fmaf(y, y, x * x));
           const float rs = __frsqrt_rn(s);
           float xi, yi, q;
           range_coords_fast(g, x, y, z, rs, xi, yi, q);
           int row, col;
-          if (range_cell_decide(g, xi, yi, q, row, col)) {
-            cell[u] = row * g.W + col;
-            key[u] = (quant_rho_guarded(v[u], s * rs) << IDX_BITS32) | (unsigned)i;
-          } else {
-            my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)i;
-          }
+          okr = range_cell_decide(g, xi, yi, q, row, col);
+          // range bucket floor(64 rho) from rho32 = s * rsqrt(s) (relative error < 4e-7)
+          const float t = (s * rs) * 64.0f;
+          const float fl = floorf(t);
+          const float fr = t - fl;
+          const float gq = fmaf(t, 1.0e-6f, 1.0e-3f);
+          okr = okr && fr > gq && fr < 1.0f - gq && t < 16382.0f;   // NaN -> false
+          cell[u] = row * g.W + col;
+          key[u] = ((unsigned)fl << IDX_BITS32) | (unsigned)i;
         }
+        defer[u] = valid && (undecided || !okr);
+        if (!valid || defer[u] || !g.enable_range) cell[u] = -1;
+        if (defer[u]) bb[u] = NO_BUCKET;
       }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (defer[u]) my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)(i0 + u * CT + tid);
       // BEV entries are appended to the bucket of their tile, one shared-memory atomic per
       // (warp, bucket): lanes with the same bucket elect a leader that reserves the slots
       if (do_bev && !(a.debug & 16)) {
@@ -396,27 +417,40 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     compute_sync();
     PROF_STAMP(1);
 
-    if (g.enable_range) {
-      // ---- S1b: deferred points, full fp64 (guard band, image border, wrap, NaN, errors)
+    // ---- S1b: deferred points, full fp64 (guard bands, image border, wrap, NaN, errors)
+    {
       const unsigned qn = misc[0];
       for (unsigned j = tid; j < qn; j += CT) {
         const unsigned i = my_queue[j];
         const float4 v = __ldg(fp + i);
-        Pt p; p.x = v.x; p.y = v.y; p.z = v.z; p.it = v.w;
-        const double rho = rho_of(p);
-        int row, col;
-        const int err = range_cell_f64(g, p, rho, row, col);
-        if (err) {
-          atomicOr(&misc[1], (unsigned)err);
-          atomicAdd(&misc[2], 1u);
-        } else {
-          const int cell = row * g.W + col;
-          const unsigned key = (quant_rho(rho) << IDX_BITS32) | i;
-          note_collision(my_cq, misc, cell, key, atomicMin(keys + cell, key));
+        if (do_bev) {
+          const int bx = bev_bin_f64((double)v.x, g.bev_start, g.bev_delta_x, g.nex);
+          const int by = bev_bin_f64((double)v.y, g.bev_start, g.bev_delta_y, g.ney);
+          if (bx >= 0 && by >= 0) {
+            const unsigned e = cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) + head;
+            const int bk = (int)(e >> bucket_shift);
+            st_u32_hint(my_buckets + ((unsigned)bk * per_cta32 + atomicAdd(&bcnt[bk], 1u)), e, keep);
+          }
+        }
+        if (g.enable_range) {
+          Pt p; p.x = v.x; p.y = v.y; p.z = v.z; p.it = v.w;
+          const double rho = rho_of(p);
+          int row, col;
+          const int err = range_cell_f64(g, p, rho, row, col);
+          if (err) {
+            atomicOr(&misc[1], (unsigned)err);
+            atomicAdd(&misc[2], 1u);
+          } else {
+            const int cell = row * g.W + col;
+            const unsigned key = (quant_rho(rho) << IDX_BITS32) | i;
+            note_collision(my_cq, misc, cell, key, atomicMin(keys + cell, key));
+          }
         }
       }
       compute_sync();
       PROF_STAMP(2);
+    }
+    if (g.enable_range) {
       // ---- S1d: exact settlement of the recorded equal-bucket candidates, 4 per thread in flight
       // (record -> key from shared memory -> candidate and holder points together -> CAS)
       {
@@ -612,7 +646,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       // entries of a tile's bucket, ENTRY_BATCH 16-byte loads per thread; slots past the end of
       // the bucket (stale) read as "not in this tile"
       auto load_batch = [&](int t, unsigned q0, uint4 (&e)[ENTRY_BATCH]) {
-        const int bkt = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
+        const int bkt = t >> (bucket_shift - a.tile_log2);
         const unsigned cnt = bcnt[bkt];
         const uint4* const bucket4 = reinterpret_cast<const uint4*>(my_buckets + (size_t)bkt * a.per_cta);
         const unsigned n4 = (cnt + 3u) >> 2;
@@ -632,7 +666,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       load_batch(0, 0u, pe);
       for (int t = 0; t < n_tiles; ++t) {
         const unsigned tlo = (unsigned)t << a.tile_log2;                 // tile coordinates of this tile
-        const int bkt = a.tiles_per_bucket == 1 ? t : t / a.tiles_per_bucket;
+        const int bkt = t >> (bucket_shift - a.tile_log2);
         const unsigned cnt = bcnt[bkt];
         const unsigned n4 = (cnt + 3u) >> 2;
         unsigned* const list_n = misc + 8 + (t & 1);   // double buffered: the other one is reset meanwhile
@@ -737,7 +771,8 @@ FusedGeom fused_geometry(const DevGrid& g) {
   o.tile_log2 = p;
   o.s2_words = (words(p) + 3) & ~3;
   const long long n_tiles = (cells + 7 + (1ll << p) - 1) >> p;
-  o.tiles_per_bucket = (int)((n_tiles + MAX_BUCKETS - 1) / MAX_BUCKETS);
+  o.tiles_per_bucket = 1;   // a power of two: the bucket of an entry is a shift
+  while ((n_tiles + o.tiles_per_bucket - 1) / o.tiles_per_bucket > MAX_BUCKETS) o.tiles_per_bucket *= 2;
   o.n_buckets = (int)((n_tiles + o.tiles_per_bucket - 1) / o.tiles_per_bucket);
   return o;
 }
