@@ -123,9 +123,7 @@ __device__ __forceinline__ bool tile_count(unsigned* tile, unsigned r) {
 }
 // The same in two steps, so that many counts can be in flight per thread.  issue: r = position
 // in the tile (>= T: not in this tile); returns (r | TC_VALID | previous byte << 24) or 0.
-// finish: the first arrival at a cell (previous byte 0) marks the cell's 32-byte sector in the
-// bitmap and, if the sector was not marked yet, appends it to the list of sectors to write;
-// an add on a byte that was already >= 128 is undone, and the >= 192 observation reported.
+// finish: an add on a byte that was already >= 128 is undone, and the >= 192 observation reported.
 constexpr unsigned TC_VALID = 1u << 23;
 __device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned r, unsigned T) {
   if (r >= T) return 0u;
@@ -133,15 +131,9 @@ __device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned r,
   const unsigned ob = (atomicAdd(tile + (r >> 2), 1u << sh) >> sh) & 0xFFu;
   return r | TC_VALID | (ob << 24);
 }
-__device__ __forceinline__ void mark_sector(unsigned* bitmap, unsigned* list, unsigned* list_n, unsigned sct) {
-  const unsigned bit = 1u << (sct & 31u);
-  if (!(atomicOr(bitmap + (sct >> 5), bit) & bit)) list[atomicAdd(list_n, 1u)] = sct;
-}
-__device__ __forceinline__ bool tile_count_finish(unsigned* tile, unsigned* bitmap, unsigned* list, unsigned* list_n,
-                                                  unsigned packed) {
+__device__ __forceinline__ bool tile_count_finish(unsigned* tile, unsigned packed) {
   if (!(packed & TC_VALID)) return false;
   const unsigned ob = packed >> 24, r = packed & (TC_VALID - 1u);
-  if (ob == 0u) { mark_sector(bitmap, list, list_n, r >> 3); return false; }
   if (ob < 128u) return false;
   atomicSub(tile + (r >> 2), 1u << ((r & 3u) * 8u));
   return ob >= 192u;
@@ -204,12 +196,13 @@ struct FusedArgs {
   int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
 };
 
-// phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph`
+// phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph` (accumulated in
+// shared memory, written out once at the end of the kernel)
 #define PROF_STAMP(ph)                                          \
   do {                                                          \
     if (a.prof && tid == 0) {                                   \
       const long long now_ = clock64();                         \
-      a.prof[(size_t)blockIdx.x * 8 + (ph)] += now_ - t_prev;   \
+      prof_acc[(ph)] += now_ - t_prev;                          \
       t_prev = now_;                                            \
     }                                                           \
   } while (0)
@@ -231,6 +224,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const int f_begin = a.fs.frame0 + blockIdx.x, f_end = a.fs.frame0 + a.fs.n_frames;
   if (tid < 65) lut[tid] = (float)a.lut64[tid];
   if (tid < 8) misc[tid] = 0u;
+  long long* const prof_acc = reinterpret_cast<long long*>(misc + 32);   // [8], thread 0 only
+  if (tid == 0)
+    for (int k = 0; k < 8; ++k) prof_acc[k] = 0;
   __syncthreads();   // the only CTA-wide barrier: the roles part here
 
   // ======================================================================== zero-fill warps
@@ -633,12 +629,11 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
     // ---- S2: BEV, one flat tile of the output at a time.  Tiles are T = 2^tile_log2 cells and
     // start on a 32-byte sector of the output (tile coordinates = frame cell + head).  Shared
-    // memory now holds: u8 counts of the tile | sector bitmap | list of non-empty sectors.
+    // memory now holds the u8 counts of the tile, nothing else: the non-empty 32-byte sectors are
+    // found by scanning the tile (one 8-byte shared load per sector, most of them zero).
     if (do_bev) {
-      const int T = 1 << a.tile_log2, tw = T >> 2, bw = (T >> 8) > 0 ? (T >> 8) : 1;
-      unsigned* const bitmap = tile + tw;      // one bit per 8-cell sector of the tile
-      unsigned* const list = bitmap + bw;      // sectors that hold a non-empty cell (<= T/8)
-      for (int w = tid; w < tw + bw; w += CT) tile[w] = 0u;
+      const int T = 1 << a.tile_log2, tw = T >> 2;
+      for (int w = tid; w < tw; w += CT) tile[w] = 0u;
       compute_sync();
       const long long B0 = E0 - head;          // global cell of tile coordinate 0
       const unsigned span_all = (unsigned)cells + head;
@@ -669,16 +664,15 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const int bkt = t >> (bucket_shift - a.tile_log2);
         const unsigned cnt = bcnt[bkt];
         const unsigned n4 = (cnt + 3u) >> 2;
-        unsigned* const list_n = misc + 8 + (t & 1);   // double buffered: the other one is reset meanwhile
         bool danger = false;
+        if (n4 == 0u && t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
         for (unsigned q0 = 0; q0 < n4; q0 += ENTRY_BATCH * CT) {
           uint4 e[ENTRY_BATCH];
-          if (q0 == 0) {
 #pragma unroll
-            for (int u = 0; u < ENTRY_BATCH; ++u) e[u] = pe[u];
-          } else {
-            load_batch(t, q0, e);
-          }
+          for (int u = 0; u < ENTRY_BATCH; ++u) e[u] = pe[u];
+          // the next batch (of this tile, else the first one of the next tile) is loaded now
+          if (q0 + ENTRY_BATCH * CT < n4) load_batch(t, q0 + ENTRY_BATCH * CT, pe);
+          else if (t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
           // stage 1: all counts go out back to back; every slot keeps (position | valid | old byte << 24)
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
@@ -687,17 +681,16 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             e[u].z = tile_count_issue(tile, e[u].z - tlo, (unsigned)T);
             e[u].w = tile_count_issue(tile, e[u].w - tlo, (unsigned)T);
           }
-          // stage 2: first arrival at a cell marks its sector; saturation fix-ups (rare)
+          // stage 2: saturation fix-ups (rare)
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].x);
-            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].y);
-            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].z);
-            danger |= tile_count_finish(tile, bitmap, list, list_n, e[u].w);
+            danger |= tile_count_finish(tile, e[u].x);
+            danger |= tile_count_finish(tile, e[u].y);
+            danger |= tile_count_finish(tile, e[u].z);
+            danger |= tile_count_finish(tile, e[u].w);
           }
         }
         if (danger) misc[3] = 1u;
-        if (t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
         // the zeros of this frame must have been issued before its non-empty sectors go out
         if (tid == 0) {
           const unsigned want = (unsigned)STORE_WARPS * (frames_done + 1);
@@ -708,34 +701,50 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         PROF_STAMP(4);
         if (misc[3]) {  // a byte may have wrapped: redo this tile with the exact (CAS) form
           compute_sync();
-          if (tid == 0) { misc[3] = 0u; *list_n = 0u; }
-          for (int w = tid; w < tw + bw; w += CT) tile[w] = 0u;
+          if (tid == 0) misc[3] = 0u;
+          for (int w = tid; w < tw; w += CT) tile[w] = 0u;
           compute_sync();
           const unsigned* const bucket = my_buckets + (size_t)bkt * a.per_cta;
           for (unsigned i = tid; i < cnt; i += CT) {
             const unsigned r = __ldcg(bucket + i) - tlo;
-            if (r < (unsigned)T && tile_count_exact(tile, r)) mark_sector(bitmap, list, list_n, r >> 3);
+            if (r < (unsigned)T) tile_count_exact(tile, r);
           }
           compute_sync();
           PROF_STAMP(5);
         }
         // write the non-empty sectors (8 cells = 32 bytes) over the zero fill; re-zero what was used
         {
-          const unsigned ln = *list_n;
-          if (tid == 0) misc[8 + ((t + 1) & 1)] = 0u;
           const long long B = B0 + tlo;                          // global cell of the tile's first cell
           const int rel_lo = t == 0 ? (int)head : 0;             // cells of THIS frame inside the tile
           const long long rem = (long long)span_all - tlo;
           const int rel_hi = rem < T ? (int)rem : T;
           uint2* const tile2 = reinterpret_cast<uint2*>(tile);
           float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
-          for (unsigned j = tid; j < ln; j += CT) {
-            const unsigned sct = list[j];
+          const int n_sct = (rel_hi + 7) >> 3;
+          // Two steps per warp, no CTA barrier in between: (1) scan the warp's sectors, 32 at a
+          // time, and list the non-empty ones (shared memory behind the tile; ~15 % of them);
+          // (2) all lanes convert and write one listed sector each.  The scan steps are light and
+          // independent, the conversion runs with full warps.
+          const int wcap = (((T >> 3) + CT - 1) / CT) * 32;
+          unsigned* const wlist = tile + (T >> 2) + (tid >> 5) * wcap;
+          unsigned wn = 0u;   // warp-uniform
+#pragma unroll 4
+          for (int base = (tid >> 5) << 5; base < n_sct; base += CT) {
+            const int sct = base + lane;
+            uint2 w = make_uint2(0u, 0u);
+            if (sct < n_sct) w = tile2[sct];
+            const bool nz = (w.x | w.y) != 0u;
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, nz);
+            if (nz) wlist[wn + (unsigned)__popc(m & lane_lt)] = (unsigned)sct;
+            wn += (unsigned)__popc(m);
+          }
+          __syncwarp();
+          for (unsigned j = lane; j < wn; j += 32u) {
+            const int sct = (int)wlist[j];
             const uint2 w = tile2[sct];
             tile2[sct] = make_uint2(0u, 0u);
-            bitmap[sct >> 5] = 0u;
             const float4 v0 = lut4(lut, w.x), v1 = lut4(lut, w.y);
-            const int c0 = (int)(sct << 3);
+            const int c0 = sct << 3;
             if (c0 >= rel_lo && c0 + 8 <= rel_hi) {
               __stcs(o4 + 2 * sct, v0);
               __stcs(o4 + 2 * sct + 1, v1);
@@ -752,20 +761,22 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       }
     }
   }
+  if (a.prof && tid == 0)
+    for (int k = 0; k < 8; ++k) a.prof[(size_t)blockIdx.x * 8 + k] += prof_acc[k];
 }
 
 // ---------------------------------------------------------------------------------------
 static int main_words_max() { return SMEM_LIMIT / 4 - SMEM_MISC_WORDS; }
 
 
-// S2 tile geometry: T = 2^p cells with T (u8 counts) + T/64 (sector bitmap) + T/2 (sector list)
+// S2 tile geometry: T = 2^p cells = T bytes (u8 counts)
 // bytes of shared memory; at most MAX_BUCKETS entry buckets, consecutive tiles share a bucket.
 FusedGeom fused_geometry(const DevGrid& g) {
   FusedGeom o;
   o.tile_log2 = 6; o.tiles_per_bucket = 1; o.n_buckets = 1; o.s2_words = 0;
   if (!g.enable_bev) return o;
   const long long cells = (long long)g.nbx * g.nby;
-  auto words = [](int p) { const long long T = 1ll << p; return (int)(T / 4 + (T / 256 > 0 ? T / 256 : 1) + T / 8); };
+  auto words = [](int p) { const long long T = 1ll << p; return (int)(T / 4 + (CT / 32) * (((T >> 3) + CT - 1) / CT) * 32); };
   int p = 6;
   while (p < 22 && (1ll << p) < cells + 8 && words(p + 1) <= main_words_max()) ++p;
   o.tile_log2 = p;
