@@ -171,6 +171,12 @@ __device__ __forceinline__ uint4 ld_u32x4_hint(const uint4* ptr, unsigned long l
   return v;
 }
 
+// 32-byte streaming store (STG.256, sm_100+): one L2 request per sector instead of two
+__device__ __forceinline__ void st_cs_f32x8(float* p, const float4 a, const float4 b) {
+  asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w),
+               "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
+}
+
 __device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
   float4 v;
   v.x = lut[min(word & 0xFFu, 64u)]; v.y = lut[min((word >> 8) & 0xFFu, 64u)];
@@ -249,25 +255,29 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const bool mine = st < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
         if (mine) a.bev[c] = 0.f;
       }
-      float4* p = reinterpret_cast<float4*>(a.bev) + W0 + st;
-      long long left = W1 - W0 - st;   // words from p to the end of the frame
+      // 32-byte stores: [W0, W1) in 16-byte words = an optional leading word to reach 32-byte
+      // alignment, then pairs, then an optional trailing word
+      long long V0 = W0, V1 = W1;
+      if ((V0 & 1) && V0 < V1) { if (st == 8) reinterpret_cast<float4*>(a.bev)[V0] = z; ++V0; }
+      if (((V1 - V0) & 1) && V0 < V1) { if (st == 9) reinterpret_cast<float4*>(a.bev)[V1 - 1] = z; --V1; }
+      float* p = a.bev + 4 * V0 + 8 * (long long)st;
+      long long left = ((V1 - V0) >> 1) - st;   // 32-byte units from p to the end of the frame
       // Paced: the frame's zeros are spread over ~85 % of one frame period of the compute warps
       // (misc[6], measured by them; FILL_PERIOD0 before the first measurement), one group of
-      // 8 x 128 16-byte stores at a time.  A burst at the full 32 B/clk of the store path would
+      // 8 x ST 32-byte stores at a time.  A burst at the full 32 B/clk of the store path would
       // fill the LSU queue in front of the compute warps' own loads / stores and, because every
       // SM does the same at the same time, saturate HBM with zeros while the point pass starves.
-      const long long groups = (W1 - W0 + 8 * ST - 1) / (8 * ST);
+      const long long groups = (((V1 - V0) >> 1) + 8 * ST - 1) / (8 * ST);
       const unsigned period = *reinterpret_cast<volatile unsigned*>(&misc[6]);
       const long long interval = groups > 0 ? ((long long)(period ? period : FILL_PERIOD0) * 27 >> 5) / groups : 0;
       long long t_next = clock64();
-      for (; left > 7 * ST; left -= 8 * ST, p += 8 * ST) {
+      for (; left > 7 * ST; left -= 8 * ST, p += 8 * 8 * ST) {
 #pragma unroll
-        for (int u = 0; u < 8; ++u) __stcs(p + u * ST, z);
+        for (int u = 0; u < 8; ++u) st_cs_f32x8(p + u * 8 * ST, z, z);
         t_next += interval;
-        if (a.debug & 2048) { while (clock64() < t_next) __nanosleep(64); }
-        else for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
+        for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
       }
-      for (; left > 0; left -= ST, p += ST) __stcs(p, z);
+      for (; left > 0; left -= ST, p += 8 * ST) st_cs_f32x8(p, z, z);
       __threadfence_block();
       __syncwarp();
       if ((tid & 31) == 0) atomicAdd(&misc[4], 1u);
@@ -497,15 +507,28 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         // One software-pipelined loop: the winners of task i+PF are prefetched into L2, those of
         // task i+1 are gathered into registers, and task i is computed and stored meanwhile.
         const int kmax = ((g.W + 3) >> 2) + 1;
-        const int ntask = kmax * g.H;
+        // H % 8 == 0: a warp takes 8 rows x 4 groups (16 cells) -- in a firing-order sweep its
+        // gathers touch 4 lines per instruction and its stores cover 192 contiguous bytes per
+        // row; otherwise one lane per row (k-major).  L2 requests, not bytes, bound this phase.
+        const bool blk8 = (g.H & 7) == 0;
+        const int nrb = g.H >> 3, nkb = (kmax + 3) >> 2;
+        const int ntask = blk8 ? nrb * nkb * 32 : kmax * g.H;
         const int hs = (g.H & (g.H - 1)) == 0 ? __ffs(g.H) - 1 : -1;
         constexpr int PF = 3;
         // first cell of task t (a multiple of 4), or -1 when t is past the end / an empty slot
         auto task_cell = [&](int t, int& r) -> int {
           r = 0;
           if (t >= ntask) return -1;
-          const int k = hs >= 0 ? t >> hs : t / g.H;
-          r = t - k * g.H;
+          int k;
+          if (blk8) {
+            const int w = t >> 5, l = t & 31;
+            const int kb = hs >= 0 ? w >> (hs - 3) : w / nrb;
+            const int rb = w - kb * nrb;
+            r = rb * 8 + (l & 7); k = kb * 4 + (l >> 3);
+          } else {
+            k = hs >= 0 ? t >> hs : t / g.H;
+            r = t - k * g.H;
+          }
           const int gid = ((r * g.W + 3) >> 2) + k;
           return gid >= (((r + 1) * g.W + 3) >> 2) ? -1 : gid << 2;
         };
@@ -586,10 +609,17 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
               __stcs(reinterpret_cast<float4*>(o + hw), make_float4(h[0], h[1], h[2], h[3]));
               __stcs(reinterpret_cast<float4*>(o + 2 * hw), make_float4(it[0], it[1], it[2], it[3]));
             } else {
-              float4* o = reinterpret_cast<float4*>(a.range + ((size_t)f * hw + c) * 3);
-              __stcs(o, make_float4(d[0], h[0], it[0], d[1]));
-              __stcs(o + 1, make_float4(h[1], it[1], d[2], h[2]));
-              __stcs(o + 2, make_float4(it[2], d[3], h[3], it[3]));
+              // 48 contiguous bytes per lane: one 32-byte (aligned) + one 16-byte store
+              float* o = a.range + ((size_t)f * hw + c) * 3;
+              const float4 q0 = make_float4(d[0], h[0], it[0], d[1]), q1 = make_float4(h[1], it[1], d[2], h[2]),
+                           q2 = make_float4(it[2], d[3], h[3], it[3]);
+              if (((uintptr_t)o & 31) == 0) {
+                st_cs_f32x8(o, q0, q1);
+                __stcs(reinterpret_cast<float4*>(o + 8), q2);
+              } else {
+                __stcs(reinterpret_cast<float4*>(o), q0);
+                st_cs_f32x8(o + 4, q1, q2);
+              }
             }
           }
           if (a.winner)
@@ -746,8 +776,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             const float4 v0 = lut4(lut, w.x), v1 = lut4(lut, w.y);
             const int c0 = sct << 3;
             if (c0 >= rel_lo && c0 + 8 <= rel_hi) {
-              __stcs(o4 + 2 * sct, v0);
-              __stcs(o4 + 2 * sct + 1, v1);
+              st_cs_f32x8(reinterpret_cast<float*>(o4 + 2 * sct), v0, v1);
             } else {  // frame head / tail: only the cells of THIS frame
               const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
@@ -793,7 +822,7 @@ bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, l
                       src.oi == 12 && ((uintptr_t)src.data & 15) == 0;
   if (!packed || g.use_extrinsic || g.n_slices || max_n > FUSED_MAX_N) return false;
   if (g.enable_range && (out.range_dtype != 0 || g.H * g.W > main_words_max())) return false;
-  if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts || ((uintptr_t)out.bev & 15) != 0)) return false;
+  if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts || ((uintptr_t)out.bev & 31) != 0)) return false;   // 32-byte stores
   if (g.enable_bev && (long long)g.nbx * g.nby > 0x7FFFFFF0ll) return false;
   return g.enable_range || g.enable_bev;
 }
