@@ -155,7 +155,7 @@ __device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
 // the CTA's BEV frames (the per-SM store path, 32 B/clk, is the longest single resource of a
 // sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
 // the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
-constexpr int STORE_WARPS = 2;
+constexpr int STORE_WARPS = 1;
 constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
 constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
 constexpr int MAX_BUCKETS = 16;                        // BEV entry buckets (consecutive tiles share one beyond 16 tiles)
@@ -170,6 +170,15 @@ __device__ __forceinline__ uint4 ld_u32x4_hint(const uint4* ptr, unsigned long l
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
   return v;
 }
+
+// TMA bulk copy shared -> global (the zero fill: its bytes do not pass through the LSU store queue
+// that the compute warps' own loads and stores wait in)
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"((unsigned)__cvta_generic_to_shared(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
 
 // 32-byte streaming store (STG.256, sm_100+): one L2 request per sector instead of two
 __device__ __forceinline__ void st_cs_f32x8(float* p, const float4 a, const float4 b) {
@@ -199,6 +208,7 @@ struct FusedArgs {
   int tile_log2;       // BEV cells per shared-memory tile = 1 << tile_log2 (>= 6)
   int tiles_per_bucket, n_buckets;
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
+  int zbuf_bytes;      // shared-memory zero buffer behind misc (source of the TMA bulk zero fill), 0 = STG fill
   int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
 };
 
@@ -229,7 +239,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const bool do_bev = g.enable_bev && a.bev;
   const int f_begin = a.fs.frame0 + blockIdx.x, f_end = a.fs.frame0 + a.fs.n_frames;
   if (tid < 65) lut[tid] = (float)a.lut64[tid];
-  if (tid < 8) misc[tid] = 0u;
+  if (tid < 16) misc[tid] = 0u;
   long long* const prof_acc = reinterpret_cast<long long*>(misc + 32);   // [8], thread 0 only
   if (tid == 0)
     for (int k = 0; k < 8; ++k) prof_acc[k] = 0;
@@ -241,6 +251,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     if (a.debug & 1) { if ((tid & 31) == 0) atomicAdd(&misc[4], 0x10000000u); return; }
     const int st = tid - CT;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    unsigned* const zbuf = smem + main_words + SMEM_MISC_WORDS;
+    for (int w = st; w < (a.zbuf_bytes >> 2); w += ST) zbuf[w] = 0u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
     unsigned k = 0;
     for (int f = f_begin; f < f_end; f += gridDim.x, ++k) {
       // at most one frame ahead of the compute warps: the fill of frame k runs next to the
@@ -254,6 +268,32 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const long long c = st < 4 ? E0 + st : 4 * W1 + (st - 4);
         const bool mine = st < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
         if (mine) a.bev[c] = 0.f;
+      }
+      if (a.zbuf_bytes && !(a.debug & 32768)) {
+        // TMA path: lane st copies the zero buffer to chunks st, st+32, ... of the frame; one
+        // group of 32 chunks at a time, spread over ~85 % of the compute warps' frame period
+        char* const gb = reinterpret_cast<char*>(a.bev) + 16 * W0;
+        const long long bytes = 16 * (W1 - W0);
+        const long long zb = a.zbuf_bytes;
+        const long long n_chunks = (bytes + zb - 1) / zb, groups = (n_chunks + 31) >> 5;
+        const unsigned period = *reinterpret_cast<volatile unsigned*>(&misc[6]);
+        const long long interval = groups > 0 ? ((long long)(period ? period : FILL_PERIOD0) * 27 >> 5) / groups : 0;
+        long long t_next = clock64();
+        for (long long c = st; c < n_chunks + st; c += 32) {   // uniform trip count over the warp
+          if (c < n_chunks) {
+            const long long off = c * zb;
+            bulk_s2g(gb + off, zbuf, (unsigned)min(zb, bytes - off));
+            bulk_commit();
+            bulk_wait<4>();
+          }
+          t_next += interval;
+          for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
+        }
+        bulk_wait<0>();   // the zeros are in memory before the non-empty sectors may be written over them
+        __threadfence();
+        __syncwarp();
+        if ((tid & 31) == 0) atomicAdd(&misc[4], 1u);
+        continue;
       }
       // 32-byte stores: [W0, W1) in 16-byte words = an optional leading word to reach 32-byte
       // alignment, then pairs, then an optional trailing word
@@ -274,8 +314,14 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       for (; left > 7 * ST; left -= 8 * ST, p += 8 * 8 * ST) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) st_cs_f32x8(p + u * 8 * ST, z, z);
-        t_next += interval;
-        for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
+        if (a.debug & 16384) {   // uniform pacing (previous scheme, kept for A/B timing)
+          t_next += interval;
+          for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
+        } else {
+          // fill only while the compute warps are in a phase that does not store to global memory
+          // themselves (point pass, fp64 pass, settlement, BEV compose), or while they wait for us
+          while (*reinterpret_cast<volatile unsigned*>(&misc[11]) == 0u) __nanosleep(400);
+        }
       }
       for (; left > 0; left -= ST, p += 8 * ST) st_cs_f32x8(p, z, z);
       __threadfence_block();
@@ -316,6 +362,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     if (tid == 0) {
       misc[7] = 0u; misc[8] = 0u; misc[9] = 0u;
       misc[5] = frames_done + 1;   // lets the zero-fill warps start on the next frame
+      misc[11] = 1u;               // fill window open (see the zero-fill warps)
       const long long now = clock64();
       if (frames_done) misc[6] = (unsigned)min(now - t_frame, 0x7FFFFFFFll);   // frame period for the fill pacing
       t_frame = now;
@@ -494,6 +541,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       }
       compute_sync();
       PROF_STAMP(7);
+      if (tid == 0) misc[11] = 0u;   // the resolve stores to global memory: fill window closed
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
         if (a.dropped) a.dropped[f] = (a.debug & 128) ? (int)misc[7] : (int)misc[2];
@@ -695,6 +743,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const unsigned cnt = bcnt[bkt];
         const unsigned n4 = (cnt + 3u) >> 2;
         bool danger = false;
+        if (tid == 0) misc[11] = 1u;   // compose works in shared memory: fill window open
         if (n4 == 0u && t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
         for (unsigned q0 = 0; q0 < n4; q0 += ENTRY_BATCH * CT) {
           uint4 e[ENTRY_BATCH];
@@ -724,7 +773,11 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         // the zeros of this frame must have been issued before its non-empty sectors go out
         if (tid == 0) {
           const unsigned want = (unsigned)STORE_WARPS * (frames_done + 1);
-          while (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) __nanosleep(200);
+          if (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) {
+            misc[11] = 2u;   // we wait for the fill: window open
+            while (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) __nanosleep(200);
+          }
+          misc[11] = 0u;     // the sector write-out stores to global memory: window closed
           __threadfence_block();
         }
         compute_sync();
@@ -860,7 +913,14 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
   a.prof = fx.prof;
   a.debug = fx.debug;
-  const size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
+  size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
+  a.zbuf_bytes = 0;
+  if (g.enable_bev && a.bev) {   // whatever shared memory is left becomes the zero buffer of the TMA fill
+    long long zb = (long long)SMEM_LIMIT - (long long)smem;
+    if (zb > 8192) zb = 8192;
+    zb &= ~127ll;
+    if (zb >= 512) { a.zbuf_bytes = (int)zb; smem += (size_t)zb; }
+  }
   k_fused_sweep<<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
   ++*launches;
   return cudaGetLastError();
