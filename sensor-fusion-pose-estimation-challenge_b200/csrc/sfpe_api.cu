@@ -289,12 +289,13 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.per_cta = (max_n + 255) & ~255ll;
     if (fx.per_cta < 256) fx.per_cta = 256;
     const FusedGeom geo = fused_geometry(g);
-    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 12);   // entry buckets + deferred queue + collision records (two levels)
+    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 12) + 256;   // entry buckets + deferred queue + collision records + claim counter
     const int grc = grow(c, &c->fused_buf, &c->fused_cap, need);
     if (grc) return grc;
     fx.entries = (unsigned*)c->fused_buf;
     fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta * geo.n_buckets;
     fx.cqueue = fx.queue + (size_t)fx.grid * fx.per_cta;
+    fx.counter = fx.cqueue + (size_t)fx.grid * fx.per_cta * 12;
     fs.frame0 = 0; fs.n_frames = n_frames;
     fx.debug = c->params.reserved[0];
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;

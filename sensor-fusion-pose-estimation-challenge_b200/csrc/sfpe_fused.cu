@@ -160,7 +160,7 @@ constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
 constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
 constexpr int MAX_BUCKETS = 16;                        // BEV entry buckets (consecutive tiles share one beyond 16 tiles)
 constexpr int NO_BUCKET = 31;
-constexpr unsigned FILL_PERIOD0 = 500000u;            // assumed frame period (SM cycles) until one is measured
+constexpr long long FILL_IN_IV = 320, FILL_OUT_IV = 1536;   // zero-fill pacing, cycles per 8 KB group
 
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -170,15 +170,6 @@ __device__ __forceinline__ uint4 ld_u32x4_hint(const uint4* ptr, unsigned long l
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(ptr), "l"(pol));
   return v;
 }
-
-// TMA bulk copy shared -> global (the zero fill: its bytes do not pass through the LSU store queue
-// that the compute warps' own loads and stores wait in)
-__device__ __forceinline__ void bulk_s2g(void* gdst, const void* ssrc, unsigned bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
-               "r"((unsigned)__cvta_generic_to_shared(ssrc)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
 
 // 32-byte streaming store (STG.256, sm_100+): one L2 request per sector instead of two
 __device__ __forceinline__ void st_cs_f32x8(float* p, const float4 a, const float4 b) {
@@ -208,7 +199,7 @@ struct FusedArgs {
   int tile_log2;       // BEV cells per shared-memory tile = 1 << tile_log2 (>= 6)
   int tiles_per_bucket, n_buckets;
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
-  int zbuf_bytes;      // shared-memory zero buffer behind misc (source of the TMA bulk zero fill), 0 = STG fill
+  unsigned* counter;   // frames claimed so far (dynamic assignment), zeroed before the launch
   int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
 };
 
@@ -237,7 +228,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const int hw = g.H * g.W;
   const long long cells = (long long)g.nbx * g.nby;
   const bool do_bev = g.enable_bev && a.bev;
-  const int f_begin = a.fs.frame0 + blockIdx.x, f_end = a.fs.frame0 + a.fs.n_frames;
+  const int f_end = a.fs.frame0 + a.fs.n_frames;
+  // zero-fill warps active?  (debug bit 0 and BEV off need none)
+  const bool self_claim = !do_bev || (a.debug & 1);
   if (tid < 65) lut[tid] = (float)a.lut64[tid];
   if (tid < 16) misc[tid] = 0u;
   long long* const prof_acc = reinterpret_cast<long long*>(misc + 32);   // [8], thread 0 only
@@ -247,20 +240,23 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
   // ======================================================================== zero-fill warps
   if (tid >= CT) {
-    if (!do_bev) return;
-    if (a.debug & 1) { if ((tid & 31) == 0) atomicAdd(&misc[4], 0x10000000u); return; }
+    if (self_claim) { if ((tid & 31) == 0) atomicAdd(&misc[4], 0x10000000u); return; }   // no fill: the compute warps claim frames themselves
     const int st = tid - CT;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    unsigned* const zbuf = smem + main_words + SMEM_MISC_WORDS;
-    for (int w = st; w < (a.zbuf_bytes >> 2); w += ST) zbuf[w] = 0u;
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    __syncwarp();
-    unsigned k = 0;
-    for (int f = f_begin; f < f_end; f += gridDim.x, ++k) {
+    for (unsigned k = 0;; ++k) {
       // at most one frame ahead of the compute warps: the fill of frame k runs next to the
       // rasterisation of frame k-1 (an unbounded run-ahead would saturate HBM with zeros first
       // and starve the point pass of every SM)
-      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(5000);
+      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(2000);
+      // frames are claimed dynamically (CTAs start staggered and drift); the claim is handed
+      // to the compute warps through misc[12 + (k & 3)] = frame + 1 (~0 = no more frames)
+      int f = 0;
+      if (st == 0) {
+        f = a.fs.frame0 + (int)atomicAdd(a.counter, 1u);
+        *reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]) = f < f_end ? (unsigned)f + 1u : ~0u;
+      }
+      f = __shfl_sync(0xFFFFFFFFu, f, 0);
+      if (f >= f_end) return;
       // this frame's BEV is cells [E0, E1) of a.bev: full 16-byte words [W0, W1) + head / tail cells
       const long long E0 = (long long)f * cells, E1 = E0 + cells;
       const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
@@ -269,32 +265,6 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const bool mine = st < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
         if (mine) a.bev[c] = 0.f;
       }
-      if (a.zbuf_bytes && !(a.debug & 32768)) {
-        // TMA path: lane st copies the zero buffer to chunks st, st+32, ... of the frame; one
-        // group of 32 chunks at a time, spread over ~85 % of the compute warps' frame period
-        char* const gb = reinterpret_cast<char*>(a.bev) + 16 * W0;
-        const long long bytes = 16 * (W1 - W0);
-        const long long zb = a.zbuf_bytes;
-        const long long n_chunks = (bytes + zb - 1) / zb, groups = (n_chunks + 31) >> 5;
-        const unsigned period = *reinterpret_cast<volatile unsigned*>(&misc[6]);
-        const long long interval = groups > 0 ? ((long long)(period ? period : FILL_PERIOD0) * 27 >> 5) / groups : 0;
-        long long t_next = clock64();
-        for (long long c = st; c < n_chunks + st; c += 32) {   // uniform trip count over the warp
-          if (c < n_chunks) {
-            const long long off = c * zb;
-            bulk_s2g(gb + off, zbuf, (unsigned)min(zb, bytes - off));
-            bulk_commit();
-            bulk_wait<4>();
-          }
-          t_next += interval;
-          for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
-        }
-        bulk_wait<0>();   // the zeros are in memory before the non-empty sectors may be written over them
-        __threadfence();
-        __syncwarp();
-        if ((tid & 31) == 0) atomicAdd(&misc[4], 1u);
-        continue;
-      }
       // 32-byte stores: [W0, W1) in 16-byte words = an optional leading word to reach 32-byte
       // alignment, then pairs, then an optional trailing word
       long long V0 = W0, V1 = W1;
@@ -302,26 +272,25 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       if (((V1 - V0) & 1) && V0 < V1) { if (st == 9) reinterpret_cast<float4*>(a.bev)[V1 - 1] = z; --V1; }
       float* p = a.bev + 4 * V0 + 8 * (long long)st;
       long long left = ((V1 - V0) >> 1) - st;   // 32-byte units from p to the end of the frame
-      // Paced: the frame's zeros are spread over ~85 % of one frame period of the compute warps
-      // (misc[6], measured by them; FILL_PERIOD0 before the first measurement), one group of
-      // 8 x ST 32-byte stores at a time.  A burst at the full 32 B/clk of the store path would
-      // fill the LSU queue in front of the compute warps' own loads / stores and, because every
-      // SM does the same at the same time, saturate HBM with zeros while the point pass starves.
-      const long long groups = (((V1 - V0) >> 1) + 8 * ST - 1) / (8 * ST);
-      const unsigned period = *reinterpret_cast<volatile unsigned*>(&misc[6]);
-      const long long interval = groups > 0 ? ((long long)(period ? period : FILL_PERIOD0) * 27 >> 5) / groups : 0;
+      // Paced at two rates, one group of 8 x 32 lanes x 32 bytes (8 KB) at a time.  The SM's
+      // path to L2 carries 32 B/clk and every phase of the compute warps that moves data itself
+      // (range resolve, BEV sector write-out) slows down by what the fill takes from it, while
+      // the point pass, the fp64 pass, the settlement and the BEV compose hardly use it: the
+      // fill runs at FILL_IN_IV cycles per group (25.6 B/clk) while misc[11] says such a phase
+      // is running, at FILL_OUT_IV (5.3 B/clk) otherwise, and unpaced when the compute warps
+      // wait for it.  (Faster inside the window and every SM -- they run in step -- saturates
+      // HBM with zeros while the point loads starve; measured optimum, profiles/README.md.)
       long long t_next = clock64();
       for (; left > 7 * ST; left -= 8 * ST, p += 8 * 8 * ST) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) st_cs_f32x8(p + u * 8 * ST, z, z);
-        if (a.debug & 16384) {   // uniform pacing (previous scheme, kept for A/B timing)
-          t_next += interval;
-          for (long long rem; (rem = t_next - clock64()) > 0;) __nanosleep((unsigned)min(rem >> 1, 100000ll) + 50u);
-        } else {
-          // fill only while the compute warps are in a phase that does not store to global memory
-          // themselves (point pass, fp64 pass, settlement, BEV compose), or while they wait for us
-          while (*reinterpret_cast<volatile unsigned*>(&misc[11]) == 0u) __nanosleep(400);
+        for (;;) {
+          const unsigned wdw = *reinterpret_cast<volatile unsigned*>(&misc[11]);
+          const long long rem = t_next + (wdw == 2u ? 0ll : wdw == 1u ? FILL_IN_IV : FILL_OUT_IV) - clock64();
+          if (rem <= 0) break;
+          __nanosleep((unsigned)min(rem >> 1, 2000ll) + 20u);
         }
+        t_next = clock64();
       }
       for (; left > 0; left -= ST, p += 8 * ST) st_cs_f32x8(p, z, z);
       __threadfence_block();
@@ -347,7 +316,24 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   unsigned frames_done = 0;
   long long t_frame = 0;
 
-  for (int f = f_begin; f < f_end; f += gridDim.x, ++frames_done) {
+  for (;; ++frames_done) {
+    if (tid == 0) {
+      unsigned c;
+      if (self_claim) {
+        const int fc = a.fs.frame0 + (int)atomicAdd(a.counter, 1u);
+        c = fc < f_end ? (unsigned)fc + 1u : ~0u;
+      } else {
+        volatile unsigned* slot = &misc[12 + (frames_done & 3u)];
+        while ((c = *slot) == 0u) __nanosleep(100);
+        *slot = 0u;
+      }
+      misc[9] = c;
+    }
+    compute_sync();
+    const unsigned claimed = misc[9];
+    compute_sync();
+    if (claimed == ~0u) break;
+    const int f = (int)claimed - 1;
     long long base, n;
     frame_span(a.fs, f, base, n);
     const float4* __restrict__ fp = a.pts + base;
@@ -906,6 +892,8 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.fs = fs;
   a.entries = fx.entries; a.queue = fx.queue; a.cqueue = reinterpret_cast<uint2*>(fx.cqueue); a.per_cta = fx.per_cta;
   a.lut64 = s.lut;
+  a.counter = fx.counter;
+  { cudaError_t e = cudaMemsetAsync(fx.counter, 0, sizeof(unsigned), st); if (e != cudaSuccess) return e; }
   a.range = (float*)out.range; a.range_layout = out.range_layout; a.winner = out.range_winner;
   a.bev = (float*)out.bev;
   a.status = out.status; a.dropped = out.dropped;
@@ -913,14 +901,7 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
   a.prof = fx.prof;
   a.debug = fx.debug;
-  size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
-  a.zbuf_bytes = 0;
-  if (g.enable_bev && a.bev) {   // whatever shared memory is left becomes the zero buffer of the TMA fill
-    long long zb = (long long)SMEM_LIMIT - (long long)smem;
-    if (zb > 8192) zb = 8192;
-    zb &= ~127ll;
-    if (zb >= 512) { a.zbuf_bytes = (int)zb; smem += (size_t)zb; }
-  }
+  const size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
   k_fused_sweep<<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
   ++*launches;
   return cudaGetLastError();

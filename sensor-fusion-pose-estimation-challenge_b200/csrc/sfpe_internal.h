@@ -60,6 +60,7 @@ struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]
   unsigned* queue;     // [grid][per_cta]
   unsigned* cqueue;    // [grid][12*per_cta] words: collision records
+  unsigned* counter;   // frame claim counter (zeroed by launch_fused)
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
   long long* prof;     // optional [grid][8] phase cycle accumulators
