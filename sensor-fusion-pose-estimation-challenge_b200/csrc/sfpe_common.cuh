@@ -212,6 +212,15 @@ __device__ __forceinline__ float asin_fast(float q) {
   return p * q;
 }
 
+// 1/sqrt(s): MUFU.RSQ (2 ulp) + one Newton step -> ~1 ulp, 5 instructions (the correctly rounded
+// __frsqrt_rn costs 23).  s = 0 / inf / NaN give NaN or 0, rejected by the guards.
+__device__ __forceinline__ float rsqrt_nr(float s) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(s));
+  const float e = fmaf(-s * r, r, 1.0f);
+  return fmaf(0.5f * r, e, r);
+}
+
 // fp32 cell coordinates (before truncation) of the range scan: xi (column), yi (row);
 // q = z/rho as computed from rs = rsqrt(x^2+y^2+z^2).
 __device__ __forceinline__ void range_coords_fast(const DevGrid& g, float x, float y, float z, float rs, float& xi,
@@ -221,16 +230,29 @@ __device__ __forceinline__ void range_coords_fast(const DevGrid& g, float x, flo
   yi = fmaf(asin_fast(q), g.inv_res_v_f, g.neg_y_min_f);
 }
 
+// floor / round-to-nearest of |t| < 2^22 on the FMA pipe (magic-number adds) instead of the
+// quarter-rate conversion unit (FRND / F2I); fi = the integer value.  Outside that range (and
+// for NaN) the results are garbage -- every caller masks such t out by its own range tests.
+__device__ __forceinline__ float floor_small(float t, int& fi) {
+  const float m = __fadd_rd(t, 12582912.0f);             // 1.5 * 2^23: ulp 1 for sums in [2^23, 2^24)
+  fi = __float_as_int(m) - 0x4B400000;
+  return m - 12582912.0f;
+}
+__device__ __forceinline__ float rint_small(float t) { return __fadd_rn(t, 12582912.0f) - 12582912.0f; }
+
 // Returns true when (row, col) = trunc(yi), trunc(xi) is PROVEN equal to the fp64 result and
 // inside the image; false -> the caller must use range_cell_f64.  Cell boundaries under
 // truncation toward zero are the NON-ZERO integers.  Written so that NaN anywhere gives false.
 __device__ __forceinline__ bool range_cell_decide(const DevGrid& g, float xi, float yi, float q, int& row, int& col) {
-  const float cx = rintf(xi), cy = rintf(yi);
+  const float cx = rint_small(xi), cy = rint_small(yi);
   const bool near_x = fabsf(xi - cx) <= EPS_COL && cx != 0.0f;
   const bool near_y = fabsf(yi - cy) <= EPS_ROW && cy != 0.0f;
-  col = (int)xi;
-  row = (int)yi;
-  return !near_x && !near_y && fabsf(q) <= MAX_SIN_EL && xi > -0.5f && yi > -0.5f && col < g.W && row < g.H;
+  // accepted coordinates are > -0.5, where truncation toward zero = max(floor, 0)
+  int fx, fy;
+  floor_small(xi, fx); floor_small(yi, fy);
+  col = max(fx, 0);
+  row = max(fy, 0);
+  return !near_x && !near_y && fabsf(q) <= MAX_SIN_EL && xi > -0.5f && yi > -0.5f && xi < (float)g.W && yi < (float)g.H;
 }
 
 // fp32 BEV bin candidate with guard band; -2 = undecided (caller uses bev_bin_f64, which also

@@ -394,7 +394,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         be[u] = 0u; bb[u] = NO_BUCKET; cell[u] = -1; key[u] = 0u;
         if (do_bev) {   // uniform
           const float tx = fmaf(x, g.bev_inv_x_f, g.bev_c0_x_f), ty = fmaf(y, g.bev_inv_y_f, g.bev_c0_y_f);
-          const float flx = floorf(tx), fly = floorf(ty);
+          int ibx, iby;
+          const float flx = floor_small(tx, ibx), fly = floor_small(ty, iby);
           const float frx = tx - flx, fry = ty - fly;
           const float nbxf = (float)g.nbx, nbyf = (float)g.nby;
           const bool inx = frx > g.bev_eps_x_f && frx < 1.0f - g.bev_eps_x_f && tx > 0.0f && tx < nbxf;   // proven bin
@@ -403,7 +404,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           const bool outy = ty < -1.0f || ty > nbyf + 1.0f;
           // NaN: neither in nor out -> undecided -> fp64 (which drops it, like histogram2d)
           undecided = !(outx || outy) && !(inx && iny);
-          const unsigned e = cells_m1 - ((unsigned)(int)flx * (unsigned)g.nby + (unsigned)(int)fly) + head;
+          const unsigned e = cells_m1 - ((unsigned)ibx * (unsigned)g.nby + (unsigned)iby) + head;
           const int bk = (int)(e >> bucket_shift);
           const bool inside = valid && inx && iny;
           be[u] = e;
@@ -412,19 +413,20 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         bool okr = true;
         if (g.enable_range) {   // uniform
           const float s = fmaf(z, z, fmaf(y, y, x * x));
-          const float rs = __frsqrt_rn(s);
+          const float rs = rsqrt_nr(s);
           float xi, yi, q;
           range_coords_fast(g, x, y, z, rs, xi, yi, q);
           int row, col;
           okr = range_cell_decide(g, xi, yi, q, row, col);
           // range bucket floor(64 rho) from rho32 = s * rsqrt(s) (relative error < 4e-7)
           const float t = (s * rs) * 64.0f;
-          const float fl = floorf(t);
+          int ifl;
+          const float fl = floor_small(t, ifl);
           const float fr = t - fl;
           const float gq = fmaf(t, 1.0e-6f, 1.0e-3f);
           okr = okr && fr > gq && fr < 1.0f - gq && t < 16382.0f;   // NaN -> false
           cell[u] = row * g.W + col;
-          key[u] = ((unsigned)fl << IDX_BITS32) | (unsigned)i;
+          key[u] = ((unsigned)ifl << IDX_BITS32) | (unsigned)i;
         }
         defer[u] = valid && (undecided || !okr);
         if (!valid || defer[u] || !g.enable_range) cell[u] = -1;
@@ -919,7 +921,7 @@ __global__ void __launch_bounds__(256) k_selftest_fastpath(const __grid_constant
     const float4 v = __ldg(pts + i);
     const float x = v.x, y = v.y, z = v.z;
     const float s = fmaf(z, z, fmaf(y, y, x * x));
-    const float rs = __frsqrt_rn(s);
+    const float rs = rsqrt_nr(s);
     float xi, yi, q;
     range_coords_fast(g, x, y, z, rs, xi, yi, q);
     Pt p; p.x = x; p.y = y; p.z = z; p.it = v.w;
