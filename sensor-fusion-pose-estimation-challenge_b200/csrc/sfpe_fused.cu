@@ -359,23 +359,20 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     PROF_STAMP(0);
 
     // ---- S1: one pass over the points
-    float4 nv4[4];   // points of the next iteration, loaded while the current one is rasterised
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const long long i = (long long)u * CT + tid;
-      nv4[u] = i < n ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    for (long long i0 = 0; i0 < n; i0 += 4 * CT) {
-      float4 v[4];
+    // (32-bit indices: n < 2^18 on this path.)  The points of the next iteration are loaded while
+    // the current one is rasterised, into the other of two register sets (no copies).
+    const int n32 = (int)n;
+    auto load4 = [&](float4 (&v)[4], int i0) {
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        v[u] = nv4[u];
-        const long long i = i0 + 4 * CT + u * CT + tid;
-        nv4[u] = i < n ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const int i = i0 + u * CT + tid;
+        v[u] = i < n32 ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      {  // L2 prefetch two iterations ahead (one 128-byte line = 8 points per thread)
-        const long long l = i0 + 3 * 4 * CT + (long long)tid * 8;
-        if (tid < 4 * CT / 8 && l < n && !(a.debug & 64)) prefetch_l2(fp + l);
+    };
+    auto rasterise4 = [&](const float4 (&v)[4], const int i0) {
+      {  // L2 prefetch three iterations ahead (one 128-byte line = 8 points per thread)
+        const int l = i0 + 3 * 4 * CT + tid * 8;
+        if (tid < 4 * CT / 8 && l < n32 && !(a.debug & 64)) prefetch_l2(fp + l);
       }
       // Per point, branch-free (so that the four points of a thread interleave): every decision
       // -- range-scan cell, range bucket, BEV bins -- is made in fp32 and PROVEN by its guard
@@ -387,8 +384,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       bool defer[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const long long i = i0 + u * CT + tid;
-        const bool valid = i < n;
+        const int i = i0 + u * CT + tid;
+        const bool valid = i < n32;
         const float x = v[u].x, y = v[u].y, z = v[u].z;
         bool undecided = false;
         be[u] = 0u; bb[u] = NO_BUCKET; cell[u] = -1; key[u] = 0u;
@@ -454,6 +451,17 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !(a.debug & 32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
 #pragma unroll
       for (int u = 0; u < 4; ++u) note_collision(my_cq, misc, cell[u], key[u], old[u]);
+    };
+    {
+      float4 va[4], vb[4];
+      load4(va, 0);
+      for (int i0 = 0; i0 < n32; i0 += 8 * CT) {
+        load4(vb, i0 + 4 * CT);
+        rasterise4(va, i0);
+        if (i0 + 4 * CT >= n32) break;
+        load4(va, i0 + 8 * CT);
+        rasterise4(vb, i0 + 4 * CT);
+      }
     }
     compute_sync();
     PROF_STAMP(1);
