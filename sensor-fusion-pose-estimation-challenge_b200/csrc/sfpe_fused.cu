@@ -100,17 +100,6 @@ __device__ __forceinline__ void settle_candidate(const float4* __restrict__ fram
   }
 }
 
-// quant_rho from the fp32 range rho32 = s*rsqrt(s) (relative error < 4e-7) when the result is
-// provably the same as quant_rho(fp64 rho); otherwise from the exact fp64 range.
-__device__ __forceinline__ unsigned quant_rho_guarded(const float4 v, float rho32) {
-  const float t = rho32 * 64.0f;
-  const float fl = floorf(t);
-  const float fr = t - fl;
-  const float gq = fmaf(t, 1.0e-6f, 1.0e-3f);
-  if (fr > gq && fr < 1.0f - gq && t < 16382.0f) return (unsigned)fl;   // NaN -> exact path
-  return quant_rho(rho_of_f4(v));
-}
-
 // Saturating u8 count inside a packed word (any count >= 63 renders as 255, so 128..255 are
 // equivalent).  Fast form: add, and take it back if the byte was already >= 128.  A byte can
 // only wrap into its neighbour if some add observes it at >= 192 first (>= 64 adds in flight on
@@ -420,7 +409,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           int ifl;
           const float fl = floor_small(t, ifl);
           const float fr = t - fl;
-          const float gq = fmaf(t, 1.0e-6f, 1.0e-3f);
+          const float gq = fmaf(t, 1.0e-6f, 1.0e-4f);
           okr = okr && fr > gq && fr < 1.0f - gq && t < 16382.0f;   // NaN -> false
           cell[u] = row * g.W + col;
           key[u] = ((unsigned)ifl << IDX_BITS32) | (unsigned)i;
@@ -941,7 +930,7 @@ __global__ void __launch_bounds__(256) k_selftest_fastpath(const __grid_constant
       m[1] = fmax(m[1], fabs((double)yi - yi64) / (double)EPS_ROW);
     }
     const float t = (s * rs) * 64.0f;
-    if (t < 16382.0f) m[2] = fmax(m[2], fabs((double)t - rho * 64.0) / (double)fmaf(t, 1.0e-6f, 1.0e-3f));
+    if (t < 16382.0f) m[2] = fmax(m[2], fabs((double)t - rho * 64.0) / (double)fmaf(t, 1.0e-6f, 1.0e-4f));
     if (g.enable_bev) {
       const float tx = fmaf(x, g.bev_inv_x_f, g.bev_c0_x_f), ty = fmaf(y, g.bev_inv_y_f, g.bev_c0_y_f);
       if (tx > 0.f && tx < (float)g.nbx) m[3] = fmax(m[3], fabs((double)tx - ((double)x - g.bev_start) / g.bev_delta_x) / (double)g.bev_eps_x_f);
