@@ -1,23 +1,29 @@
 // Fused "one sweep per SM" path (the hot path of bench.py).
 //
-// A persistent CTA (1024 threads, ~226 KB dynamic shared memory, one CTA per SM) takes whole
-// sweeps.  Per sweep:
+// A persistent CTA (512 threads = 15 compute warps + 1 zero-fill warp, 128 registers, ~227 KB
+// dynamic shared memory, one CTA per SM) claims whole sweeps from a global counter.  Per sweep:
 //   S0  range-scan winner keys (H*W x u32) are initialised in shared memory
-//   S1  one coalesced pass over the sweep's float4 points (16 B/point from HBM):
-//         - fp64 range rho (exact numpy order), fp32 cell with guard band -> 32-bit packed key
-//           [14-bit quantised rho | 18-bit point index] -> shared-memory atomicMin; equal
-//           prefixes are settled exactly on the fp64 rho (CAS loop); guard-band / out-of-image
-//           points go to a deferred queue that is re-done in fp64 (S1b)
-//         - exact BEV bin (np.arange edges in fp64) -> flat output cell written to an entry list
-//           (L2 evict_last: it is re-read once per BEV tile)
-//   S1c range scan resolved from shared memory, column-major over the image so that the winner
-//       gathers of a warp hit neighbouring points; 3 channels written once with 16-byte stores
-//   S2  BEV composed in shared memory as saturating u8 counts, one flat tile of the output at a
-//       time: filter the entry list, then write the 32-byte sectors that hold a non-empty cell
-//   ZF  the BEV image is >95 % zeros and the per-SM store path (~30 B/clk) is the longest single
-//       resource of a sweep, so the zero fill of the frame is not a phase: every thread pumps a
-//       few 16-byte zero stores per iteration of S1 / S1c / S2-compose, and only catches up (if
-//       needed) before the non-empty sectors of a tile are written over the zeros.
+//   S1  point pass, 4 points per thread and iteration in two register sets (the next iteration's
+//       16-byte point loads are in flight while this one is rasterised; L2 prefetch 3 ahead).
+//       Branch-free: every decision (range cell, range bucket, BEV bins) is made in fp32 and
+//       proven by a guard band; a point with an unproven decision is deferred as a whole.
+//         - key [14-bit floor(64 rho) | 18-bit point index] -> shared-memory atomicMin
+//         - BEV entry (flat output cell) appended to the bucket of its tile (one shared atomic
+//           per (warp, bucket), L2 evict_last: it is read back once in S2)
+//   S1b deferred points (~0.4 %) in fp64 exactly as numpy evaluates them
+//   S1d equal-bucket keys settled under the exact order (rho fp64, index)
+//   S1c range scan resolved from shared memory: a warp takes 8 rows x 16 cells, gathers the
+//       winners (prefetched into L2 three tasks ahead, loaded one task ahead) and writes 48
+//       contiguous bytes per lane with one 32-byte and one 16-byte store
+//   S2  BEV, one flat tile (2^17 cells) of the output at a time: u8 counts composed in shared
+//       memory from the tile's bucket, then each warp lists the non-empty 32-byte sectors of
+//       its part of the tile and writes them with one 32-byte store each over the zero fill
+//   ZF  the zero-fill warp streams the frame's zeros (STG.256), fast while the compute warps are
+//       in S1 / S1b / S1d / S2-compose (which hardly use the SM's path to L2), slowly while they
+//       store themselves (S1c, S2 write-out), unpaced when they wait for it.
+// What bounds it (profiles/README.md): the SM's port to L2 moves one request (<= 128-byte line)
+// per ~4 cycles whatever its size, so the phases are tuned for few, full requests, and the
+// zero fill's 45 k lines per sweep are placed where the other phases issue the fewest.
 // HBM traffic: points read once (+ the winner gather), range written once, BEV written once plus
 // the non-empty sectors a second time.
 #include "sfpe_internal.h"
@@ -29,7 +35,7 @@ constexpr int IDX_BITS32 = 18;                       // point index bits of the 
 constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
-constexpr int SMEM_MISC_WORDS = 128;                 // LUT (65 floats) + counters
+constexpr int SMEM_MISC_WORDS = 256;                 // LUT (65 floats) | 16 counters | 16 profile words | bucket counts
 constexpr int ENTRY_BATCH = 3;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
@@ -145,10 +151,10 @@ __device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
 // sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
 // the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
 constexpr int STORE_WARPS = 1;
-constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 896 compute threads
-constexpr int ST = 32 * STORE_WARPS;                   // 128 zero-fill threads
-constexpr int MAX_BUCKETS = 16;                        // BEV entry buckets (consecutive tiles share one beyond 16 tiles)
-constexpr int NO_BUCKET = 31;
+constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 480 compute threads
+constexpr int ST = 32 * STORE_WARPS;                   // 32 zero-fill threads
+constexpr int MAX_BUCKETS = 64;                        // BEV entry buckets (consecutive tiles share one beyond 64 tiles)
+constexpr int NO_BUCKET = 255;
 constexpr long long FILL_IN_IV = 320, FILL_OUT_IV = 1536;   // zero-fill pacing, cycles per 8 KB group
 
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
@@ -222,7 +228,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const bool self_claim = !do_bev || (a.debug & 1);
   if (tid < 65) lut[tid] = (float)a.lut64[tid];
   if (tid < 16) misc[tid] = 0u;
-  long long* const prof_acc = reinterpret_cast<long long*>(misc + 32);   // [8], thread 0 only
+  long long* const prof_acc = reinterpret_cast<long long*>(misc + 16);   // [8], thread 0 only
   if (tid == 0)
     for (int k = 0; k < 8; ++k) prof_acc[k] = 0;
   __syncthreads();   // the only CTA-wide barrier: the roles part here
@@ -291,7 +297,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
   // ======================================================================== compute warps
   unsigned* const my_buckets = a.entries + (size_t)blockIdx.x * a.n_buckets * a.per_cta;   // [bucket][per_cta]
-  unsigned* const bcnt = misc + 16;   // entries per bucket
+  unsigned* const bcnt = misc + 32;   // entries per bucket [MAX_BUCKETS]
   const int lane = tid & 31;
   const unsigned per_cta32 = (unsigned)a.per_cta;
   const unsigned lane_lt = (1u << lane) - 1u;
@@ -333,7 +339,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     if (g.enable_range)
       for (int i = tid; i < hw; i += CT) keys[i] = KEY32_EMPTY;
     if (tid < 4) misc[tid] = 0u;
-    if (tid >= 16 && tid < 16 + MAX_BUCKETS) misc[tid] = 0u;
+    if (tid >= 32 && tid < 32 + MAX_BUCKETS) misc[tid] = 0u;
     if (tid == 0) {
       misc[7] = 0u; misc[8] = 0u; misc[9] = 0u;
       misc[5] = frames_done + 1;   // lets the zero-fill warps start on the next frame
