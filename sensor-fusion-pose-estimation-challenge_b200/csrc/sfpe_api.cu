@@ -105,7 +105,6 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
   g->use_extrinsic = p->use_extrinsic != 0;
   memcpy(g->M, p->extrinsic, sizeof(g->M));
   if (p->n_slices < 0 || p->n_slices > SFPE_MAX_SLICES) return SFPE_ERR_INVALID_ARG;
-  if (p->n_slices > 0) return SFPE_ERR_UNSUPPORTED;   // MV3D height / intensity BEV channels: not built yet
   g->n_slices = g->enable_bev ? p->n_slices : 0;
   for (int i = 0; i <= p->n_slices; ++i) {
     g->slice_edges[i] = p->slice_edges[i];

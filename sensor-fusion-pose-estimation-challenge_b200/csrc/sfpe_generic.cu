@@ -37,6 +37,15 @@ __device__ __noinline__ void settle_collision(const DevGrid& g, const PointSrc& 
   }
 }
 
+// order-preserving u32 encoding of a float (0 is below every encoded value except -NaN)
+__device__ __forceinline__ unsigned ord_f32(float v) {
+  const unsigned b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float unord_f32(unsigned o) {
+  return __uint_as_float((o & 0x80000000u) ? (o & 0x7FFFFFFFu) : ~o);
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(256) k_project(const __grid_constant__ DevGrid g, const __grid_constant__ PointSrc src, const FrameSet fs,
                                                  const Scratch s, int* __restrict__ status,
@@ -68,7 +77,21 @@ __global__ void __launch_bounds__(256) k_project(const __grid_constant__ DevGrid
     if (g.enable_bev) {
       const int bx = bev_bin_f64(p.x, g.bev_start, g.bev_delta_x, g.nex);
       const int by = bev_bin_f64(p.y, g.bev_start, g.bev_delta_y, g.ney);
-      if (bx >= 0 && by >= 0) atomicAdd(counts + (size_t)bx * g.nby + by, 1u);
+      if (bx >= 0 && by >= 0) {
+        const size_t cell = (size_t)bx * g.nby + by;
+        atomicAdd(counts + cell, 1u);
+        if (g.n_slices) {   // extension: per-slice max z, highest point of the cell
+          const size_t cells = (size_t)g.nbx * g.nby;
+          int sl = -1;
+          for (int k = 0; k < g.n_slices; ++k)
+            if (p.z >= g.slice_edges[k] && p.z < g.slice_edges[k + 1]) sl = k;
+          if (sl >= 0) {
+            const unsigned oz = ord_f32((float)p.z);
+            atomicMax(s.slice_max + ((size_t)lf * g.n_slices + sl) * cells + cell, oz);
+            atomicMax(s.top + (size_t)lf * cells + cell, ((unsigned long long)oz << 32) | (0xFFFFFFFFu - (unsigned)i));
+          }
+        }
+      }
     }
   }
   if (err_acc) {
@@ -143,6 +166,38 @@ __global__ void __launch_bounds__(256) k_resolve_bev(const DevGrid g, const Fram
       else ((double*)out.bev)[(size_t)f * cells + c] = v;
     }
     if (out.bev_counts) out.bev_counts[(size_t)f * cells + sc] = cnt;
+  }
+}
+
+// Extension outputs (MV3D 3.1; no reference code): per height slice the max z of the
+// slice's points of the cell (empty: the slice's lower edge), and the intensity of the highest
+// point of the cell within [edge 0, edge M) (ties on z: lowest index; empty: 0).  Both reversed
+// on both axes like the density.  Scratch is reset in the same pass.
+template <int KIND>
+__global__ void __launch_bounds__(256) k_resolve_bev_ext(const __grid_constant__ DevGrid g, const __grid_constant__ PointSrc src,
+                                                         const FrameSet fs, const Scratch s, const DevOut out) {
+  const int lf = blockIdx.y;
+  const int f = fs.frame0 + lf;
+  long long base, n;
+  frame_span(fs, f, base, n);
+  const size_t cells = (size_t)g.nbx * g.nby;
+  for (size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x; c < cells; c += (size_t)gridDim.x * blockDim.x) {
+    const size_t sc = cells - 1 - c;
+    for (int k = 0; k < g.n_slices; ++k) {
+      unsigned* a = s.slice_max + ((size_t)lf * g.n_slices + k) * cells + sc;
+      const unsigned o = *a;
+      *a = 0u;
+      if (out.bev_height) out.bev_height[((size_t)f * g.n_slices + k) * cells + c] = o ? unord_f32(o) : (float)g.slice_edges[k];
+    }
+    unsigned long long* t = s.top + (size_t)lf * cells + sc;
+    const unsigned long long key = *t;
+    *t = 0ull;
+    float it = 0.f;
+    if (key) {
+      const unsigned idx = 0xFFFFFFFFu - (unsigned)(key & 0xFFFFFFFFull);
+      it = (float)load_point<KIND>(g, src, base + idx).it;
+    }
+    if (out.bev_intensity) out.bev_intensity[(size_t)f * cells + c] = it;
   }
 }
 
@@ -227,6 +282,11 @@ cudaError_t launch_generic_chunk(const DevGrid& g, const PointSrc& src, const Fr
     const dim3 grid_b(blocks_for((size_t)g.nbx * g.nby, 256 * 4, 65535), fs.n_frames);
     k_resolve_bev<<<grid_b, 256, 0, st>>>(g, fs, s, out);
     ++*launches;
+    if (g.n_slices) {
+      if (packed) k_resolve_bev_ext<SRC_PACKED_F32><<<grid_b, 256, 0, st>>>(g, src, fs, s, out);
+      else k_resolve_bev_ext<SRC_GENERIC><<<grid_b, 256, 0, st>>>(g, src, fs, s, out);
+      ++*launches;
+    }
   }
   return cudaGetLastError();
 }

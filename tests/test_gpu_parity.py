@@ -355,3 +355,37 @@ def test_streaming_entry_matches_oracle(pkg, synth):
     with pytest.raises(IndexError):
         sv(synth.make_pointcloud2_blob(bad).tobytes())
     sv.close()
+
+
+# ---------------------------------------------------------------- extension: MV3D height slices + intensity (parity unpinned)
+@pytest.mark.parametrize("with_extrinsic", [False, True])
+def test_extension_height_slices_and_intensity(pkg, synth, with_extrinsic):
+    """no reference code exists; the oracle's definition is the contract
+    (per slice max z, empty = slice floor; intensity of the highest point, tie -> lowest index).
+    Default-off: the drop-in outputs (range scan, density) are unchanged when it is on."""
+    import torch
+    edges = [-2.0, -1.0, 0.0, 1.0, 3.0]
+    sweeps = [synth.make_sweep("hdl32", seed=70, n_az=700), synth.make_sweep("hdl64", seed=71, n_az=300, shuffle=True)]
+    # duplicates of the highest points: ties on z must go to the lowest index
+    dup = sweeps[0][np.argsort(-sweeps[0][:, 2])[:50]].copy()
+    dup[:, 3] += 1.0
+    sweeps[0] = np.concatenate([sweeps[0], dup]).astype(np.float32)
+    M = None
+    if with_extrinsic:
+        M = np.array([[0.999, -0.04, 0.0, 0.3], [0.04, 0.999, 0.0, -0.2], [0.0, 0.0, 1.0, 0.5]])
+    pr = pkg.LidarProjector(device=0, bev_res=(0.5, 0.5), slice_edges=edges, extrinsic=M, enable_range=False)
+    offs = np.cumsum([0] + [len(s) for s in sweeps]).astype(np.int64)
+    out = pr.project(torch.from_numpy(np.concatenate(sweeps)).cuda(), n_frames=len(sweeps),
+                     frame_offsets=torch.from_numpy(offs).cuda(), max_n=max(len(s) for s in sweeps))
+    torch.cuda.synchronize()
+    assert pr.last_path == "generic"
+    for f, s in enumerate(sweeps):
+        P = _P(s)
+        if with_extrinsic:   # the transformed cloud is again a float32 cloud (sfpe_common.cuh apply_extrinsic)
+            xyz = (M[:, 0] * P[:, 0:1] + M[:, 1] * P[:, 1:2]) + M[:, 2] * P[:, 2:3] + M[:, 3]
+            P[:, :3] = xyz.astype(np.float32).astype(np.float64)
+        h, it = lo.bev_height_intensity(P, (0.5, 0.5), 120, edges)
+        assert np.array_equal(out["bev_height"][f].cpu().numpy(), h.astype(np.float32))
+        assert np.array_equal(out["bev_intensity"][f].cpu().numpy(), it.astype(np.float32))
+        np.testing.assert_allclose(out["bev"][f].cpu().numpy(), lo.bev_density(P, (0.5, 0.5), 120), rtol=DENSITY_RTOL)
+    pr.close()

@@ -82,3 +82,20 @@ def test_oracle_equals_live_reference(synth):
     for k in port:
         assert np.array_equal(port[k], ref[k + "_float"])
     assert np.array_equal(lo.port_generate_birds_eye_view(P, (2, 2)), rl.bev_density(P, (2, 2)))
+
+
+def test_extension_definition_hand_case():
+    """MV3D extension (parity unpinned): the definition the GPU tests compare against."""
+    from oracle import lidar_oracle as lo
+    # 2 m cells: x in [0,2) -> bin 60, y in [0,2) -> bin 60 of 119; output is reversed on both axes
+    P = np.array([[0.5, 0.5, -0.5, 10.0, 0], [1.0, 1.5, 0.7, 20.0, 0], [1.2, 0.2, 0.7, 30.0, 0],   # same cell
+                  [0.5, 0.5, 5.0, 40.0, 0],                                                           # above the last edge
+                  [-3.0, 0.5, 0.2, 50.0, 0]])                                                         # another cell
+    h, it = lo.bev_height_intensity(P, (2, 2), 120, [-1.0, 0.0, 1.0])
+    assert h.shape == (2, 119, 119) and it.shape == (119, 119)
+    c = (118 - 60, 118 - 60)
+    assert h[0][c] == -0.5 and h[1][c] == np.float64(0.7)
+    assert it[c] == 20.0                      # highest point, tie on z -> lowest index
+    c2 = (118 - 58, 118 - 60)
+    assert h[0][c2] == -1.0 and h[1][c2] == 0.2 and it[c2] == 50.0
+    assert (h[0] == -1.0).sum() == 119 * 119 - 1 and (it != 0).sum() == 2
