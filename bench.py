@@ -268,7 +268,8 @@ def run_ours(a):
             "metric": "lidar sweeps/s (BEV+range projection)", "value": value, "unit": "sweeps/s",
             "points_per_s": value * a.n_pts,
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": total_ms / a.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 decisions proven by guard bands, f64 where unproven (bit-exact with the reference's f64); f32 outputs",
             "data": "synthetic", "config": workload_config(a),
             "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad, "dropped_mean": dropped_mean,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
