@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsfpe.so")
+# SFPE_LIB: another build of the same library (tuning experiments, tools/variants.sh)
+LIB_PATH = os.environ.get("SFPE_LIB") or os.path.join(_HERE, "libsfpe.so")
 
 SFPE_F32, SFPE_F64 = 0, 1
 RANGE_CHW, RANGE_HWC = 0, 1

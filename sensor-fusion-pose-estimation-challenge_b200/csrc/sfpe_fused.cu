@@ -13,7 +13,7 @@
 //   S1b deferred points (~0.4 %) in fp64 exactly as numpy evaluates them
 //   S1d equal-bucket keys settled under the exact order (rho fp64, index)
 //   S1c range scan resolved from shared memory: a warp takes 8 rows x 16 cells, gathers the
-//       winners (prefetched into L2 three tasks ahead, loaded one task ahead) and writes 48
+//       winners (prefetched into L2 two tasks ahead, loaded one task ahead) and writes 48
 //       contiguous bytes per lane with one 32-byte and one 16-byte store
 //   S2  BEV, one flat tile (2^17 cells) of the output at a time: u8 counts composed in shared
 //       memory from the tile's bucket, then each warp lists the non-empty 32-byte sectors of
@@ -553,7 +553,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const int nrb = g.H >> 3, nkb = (kmax + 3) >> 2;
         const int ntask = blk8 ? nrb * nkb * 32 : kmax * g.H;
         const int hs = (g.H & (g.H - 1)) == 0 ? __ffs(g.H) - 1 : -1;
-        constexpr int PF = 3;
+        constexpr int PF = 2;
         // first cell of task t (a multiple of 4), or -1 when t is past the end / an empty slot
         auto task_cell = [&](int t, int& r) -> int {
           r = 0;
