@@ -19,8 +19,8 @@
 //       memory from the tile's bucket, then each warp lists the non-empty 32-byte sectors of
 //       its part of the tile and writes them with one 32-byte store each over the zero fill
 //   ZF  the zero-fill warp streams the frame's zeros (STG.256), fast while the compute warps are
-//       in S1 / S1b / S1d / S2-compose (which hardly use the SM's path to L2), slowly while they
-//       store themselves (S1c, S2 write-out), unpaced when they wait for it.
+//       in S1 / S2-compose (which hardly use the SM's path to L2), slowly while they wait on loads
+//       (S1b, S1d) or store themselves (S1c, S2 write-out), unpaced when they wait for it.
 // What bounds it (profiles/README.md): the SM's port to L2 moves one request (<= 128-byte line)
 // per ~4 cycles whatever its size, so the phases are tuned for few, full requests, and the
 // zero fill's 45 k lines per sweep are placed where the other phases issue the fewest.
@@ -151,6 +151,7 @@ __device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
 // sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
 // the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
 constexpr int STORE_WARPS = 1;
+static_assert(STORE_WARPS == 1, "the frame claim is made by lane 0 of THE zero-fill warp");
 constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 480 compute threads
 constexpr int ST = 32 * STORE_WARPS;                   // 32 zero-fill threads
 constexpr int MAX_BUCKETS = 64;                        // BEV entry buckets (consecutive tiles share one beyond 64 tiles)
@@ -270,7 +271,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       // Paced at two rates, one group of 8 x 32 lanes x 32 bytes (8 KB) at a time.  The SM's
       // path to L2 carries 32 B/clk and every phase of the compute warps that moves data itself
       // (range resolve, BEV sector write-out) slows down by what the fill takes from it, while
-      // the point pass, the fp64 pass, the settlement and the BEV compose hardly use it: the
+      // the point pass and the BEV compose hardly use it (and do not wait on loads): the
       // fill runs at FILL_IN_IV cycles per group (25.6 B/clk) while misc[11] says such a phase
       // is running, at FILL_OUT_IV (5.3 B/clk) otherwise, and unpaced when the compute warps
       // wait for it.  (Faster inside the window and every SM -- they run in step -- saturates
@@ -460,6 +461,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     }
     compute_sync();
     PROF_STAMP(1);
+    if (tid == 0) misc[11] = 0u;   // the fp64 pass and the settlement wait on loads: fill window closed
 
     // ---- S1b: deferred points, full fp64 (guard bands, image border, wrap, NaN, errors)
     {
@@ -532,7 +534,6 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       }
       compute_sync();
       PROF_STAMP(7);
-      if (tid == 0) misc[11] = 0u;   // the resolve stores to global memory: fill window closed
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
         if (a.dropped) a.dropped[f] = (a.debug & 128) ? (int)misc[7] : (int)misc[2];
