@@ -90,7 +90,7 @@ typedef struct {
   int32_t key_prefix_bits; /* 0 = auto.  Bits of the fp64 range kept in the packed winner key;
                               small values force the exact-compare slow path (tests). */
   int32_t path;            /* 0 = auto, 1 = generic global-scratch kernels, 2 = fused cluster kernel */
-  int32_t reserved[6];
+  int32_t reserved[6];   /* must be 0 ([0]: kernel ablation bits for timing experiments, results invalid) */
 } sfpe_params;
 
 /* Where the points of a batch live (device memory).  Point p of the batch is at

@@ -196,7 +196,12 @@ struct FusedArgs {
   int tiles_per_bucket, n_buckets;
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
   unsigned* counter;   // frames claimed so far (dynamic assignment), zeroed before the launch
-  int debug;           // bit 0: skip the zero fill (timing experiments; output then invalid)
+  // sfpe_params.reserved[0]: ablation bits for timing experiments (tools/ablate.sh); the output is
+  // INVALID when any of 1..64, 256, 512 is set.  1 no zero fill, 2 no range stores, 4 no winner
+  // gather, 8 no resolve prefetch, 16 no BEV entry append, 32 no range atomics, 64 no point
+  // prefetch, 128 report the collision record count in `dropped`, 256 settle: loads only,
+  // 512 settle: no point loads
+  int debug;
 };
 
 // phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph` (accumulated in
