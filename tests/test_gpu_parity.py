@@ -228,7 +228,7 @@ def test_fused_path_many_frames_uniform_chw(pkg, synth):
         _check_frame(res, f, sweeps[f], layout="chw")
 
 
-@pytest.mark.parametrize("res_m", [(2, 2), (0.5, 0.25), (0.1, 0.1)])
+@pytest.mark.parametrize("res_m", [(2, 2), (0.5, 0.25), (0.1, 0.1), (0.05, 0.05)])   # 0.05: 176 tiles, 4 per bucket (C5)
 def test_fused_path_other_bev_resolutions(pkg, synth, res_m):
     sweeps = [synth.make_sweep("vls128", seed=40, n_az=400, near_heavy=True), synth.make_sweep("hdl32", seed=41),
               synth.make_sweep("hdl32", seed=42, n_az=3)]
