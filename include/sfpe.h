@@ -16,6 +16,9 @@
  *   sfpe_decode_pointcloud2   sensor_msgs.point_cloud2.read_points + np.array(list(..)) at
  *                             team_sf_rosnode/scripts/lidar_predict.py:64-65,
  *                             process/extract_rosbag.py:165-166, train/predict.py:373-374
+ *   sfpe_invariant_mask_update  process/create_lidar_invariant_mask.py:44-62
+ *   sfpe_roll_width           train/loader.py:31-57 (data_random_rotate's np.roll)
+ *   sfpe_back_project         train/predict.py:230-293 (back_project_2D_2_3D)
  *   sfpe_params defaults      process/globals.py:3-13 (RES, VFOV, LIDAR_MIN_HEIGHT, ...)
  *
  * Conventions: every function returns 0 (SFPE_OK) or a negative sfpe_status; nothing throws
@@ -172,6 +175,40 @@ SFPE_API int sfpe_colormap(sfpe_ctx* ctx, const void* d_img, int32_t dtype, int6
 /* same, HOST in / HOST out, synchronised */
 SFPE_API int sfpe_colormap_host(sfpe_ctx* ctx, const void* h_img, int32_t dtype, int64_t n, int32_t cmap,
                        int32_t autoscale, double vmin, double vmax, uint8_t* h_rgb);
+
+/* ---- consumers of the range scan, kept on the device ---------------- */
+
+/* Invariant-pixel mask (process/create_lidar_invariant_mask.py:44-62, update_invariant_pixels_new:
+ * `np.logical_and(mask, reference == float_pixels, mask)` once per frame):
+ *   d_mask[p] = 0 where d_frames[f*frame_stride + p*pix_stride] != d_ref[p*pix_stride] for any f
+ * (NaN != NaN as in numpy); other mask bytes are left as they are, so the caller starts from 1s.
+ * Strides are in ELEMENTS of `dtype`; pix_stride 1 with n_pix = 32*1801*3 walks an HWC frame whole,
+ * pix_stride 3 walks one channel of it.  d_mask: n_pix bytes. */
+SFPE_API int sfpe_invariant_mask_update(sfpe_ctx* ctx, const void* d_ref, const void* d_frames, int32_t dtype,
+                               int64_t n_frames, int64_t frame_stride, int64_t n_pix, int32_t pix_stride,
+                               uint8_t* d_mask, void* stream);
+
+/* Roll augmentation (train/loader.py:31-57, data_random_rotate: `np.roll(image, rotate_by, axis=1)`
+ * on (height, width, channels) images and on the reshaped labels):
+ *   d_out[f][h][(w + d_shift[f]) mod width] = d_in[f][h][w], pixels of pix_bytes bytes (multiple of 4).
+ * Out of place (the reference copies the rolled array back over the input). d_shift: device int32[n_frames]. */
+SFPE_API int sfpe_roll_width(sfpe_ctx* ctx, const void* d_in, void* d_out, int64_t n_frames, int32_t height,
+                    int32_t width, int32_t pix_bytes, const int32_t* d_shift, void* stream);
+
+/* Back-projection of cluster centroids (train/predict.py:230-293, back_project_2D_2_3D).  Per item i:
+ * if the pixel under the centroid is not valid (distance > 0 and height > min_height) and the box
+ * has non-zero left/right, the centroid moves to the valid pixel of the box nearest to it (first in
+ * row-major order on ties), or centroid and box are zeroed when the box has none; then, unless the
+ * centroid is (0,0), xyz = ((d+0.75) cos t, -(d+0.75) sin t, height, 0) with t = (cx + x_min)*res_rad.
+ * d_centroids [n][2] (x=column, y=row) and d_bboxes [n][4] (left, top, right, bottom) are float64 and
+ * updated in place like the reference's arrays; d_xyz [n][4] float64; d_status [n]: 0 kept, 1 moved,
+ * 2 zeroed, 3 centroid/box outside the image (reference would raise or wrap; item left untouched).
+ * d_distance / d_height: item i's image at + i*frame_stride, pixel (r,c) at (r*width+c)*pix_stride,
+ * ELEMENTS of `dtype`.  Pixel choice is exact; x,y go through the device's fp64 cos/sin (<= 2 ulp). */
+SFPE_API int sfpe_back_project(sfpe_ctx* ctx, double* d_centroids, double* d_bboxes, int64_t n,
+                      const void* d_distance, const void* d_height, int32_t dtype, int64_t frame_stride,
+                      int32_t pix_stride, int32_t height, int32_t width, double min_height, double x_min,
+                      double res_rad, double* d_xyz, int32_t* d_status, void* stream);
 
 /* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
 SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);

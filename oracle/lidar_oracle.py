@@ -236,3 +236,55 @@ def port_generate_birds_eye_view(points, res, max_range=120, python_loop=True):
         nz = ch > 0
         ch[nz] = 255 * np.minimum(np.log(ch[nz] + 1) / np.log(64), 1)
     return np.flipud(np.fliplr(ch))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Consumers of the range scan.  numpy restatements; test infrastructure only.
+# ---------------------------------------------------------------------------------------------------------
+
+def invariant_mask_update(mask, reference, float_pixels):
+    """process/create_lidar_invariant_mask.py:59-62: the mask keeps only pixels equal to the reference
+    frame in every frame seen so far (elementwise ==, so NaN never matches).  In place, returns mask."""
+    same = reference == float_pixels                                   # :61
+    np.logical_and(mask, same, mask)                                   # :62
+    return mask
+
+
+def roll_width(image, rotate_by):
+    """train/loader.py:47-50: np.roll of an (height, width, channels) array along its width."""
+    return np.roll(image, rotate_by, axis=1)
+
+
+def back_project(centroids, bboxes, distance_data, height_data):
+    """train/predict.py:230-293 (back_project_2D_2_3D).  centroids (B,2) [column, row], bboxes (B,4)
+    [left, top, right, bottom], both float and updated IN PLACE like the reference; distance_data /
+    height_data (B,h,w).  Returns xyz (B,4) float64 (last column stays 0).  Boxes are expected inside the
+    image (the reference's slices would silently clip and then unravel with the unclipped shape)."""
+    from math import sin, cos
+    B, h, w = distance_data.shape
+    xyz = np.zeros((B, 4))                                             # :231
+    valid = np.logical_and(distance_data > 0, height_data > LIDAR_MIN_HEIGHT)   # :236
+    for i in range(B):
+        cx, cy = int(centroids[i, 0]), int(centroids[i, 1])
+        if (not valid[i, cy, cx]) and bboxes[i, 0] != 0 and bboxes[i, 2] != 0:  # :243
+            left, right = int(bboxes[i, 0]), int(bboxes[i, 2]) + 1     # :245-248
+            top, bottom = int(bboxes[i, 1]), int(bboxes[i, 3]) + 1
+            rows, cols = np.mgrid[top:bottom, left:right]
+            d = np.sqrt((cols - cx) * (cols - cx) + (rows - cy) * (rows - cy)).astype(np.float64)   # :251-253
+            d = np.where(valid[i, top:bottom, left:right], d, 10e7)    # :255
+            k = int(np.argmin(d))                                      # :256 first minimum in row-major order
+            if d.flat[k] == 10e7:                                      # :262-269 nothing valid in the box
+                centroids[i, :] = 0
+                bboxes[i, :] = 0
+            else:
+                r, c = divmod(k, right - left)                         # :271
+                centroids[i, 1], centroids[i, 0] = r + top, c + left   # :272-275
+        if not (centroids[i, 0] == 0 and centroids[i, 1] == 0):        # :277
+            dist = float(distance_data[i, int(centroids[i, 1]), int(centroids[i, 0])])   # :278
+            hgt = float(height_data[i, int(centroids[i, 1]), int(centroids[i, 0])])      # :279
+            theta = (centroids[i, 0] + X_MIN) * RES_RAD[1]             # :280
+            dist += 0.75                                               # :283
+            xyz[i, 0] = dist * cos(theta)                              # :285
+            xyz[i, 1] = -dist * sin(theta)                             # :286
+            xyz[i, 2] = hgt                                            # :287
+    return xyz

@@ -110,3 +110,25 @@ def bev_density(points, res, max_range=120):
     _Capture.last = None
     bev.generate_birds_eye_view(points, 0, res, max_range=max_range, cmap="gray")
     return _Capture.last
+
+
+def back_project_fn():
+    """The reference's back_project_2D_2_3D (train/predict.py:230-293), unmodified.  predict.py as a whole
+    needs rosbag, cv2, keras and python-2 print statements, so only that function's own source lines are
+    compiled, in a namespace holding exactly the names it uses (numpy, math.sin/cos and the constants of
+    process/globals.py)."""
+    if "bp" in _cache:
+        return _cache["bp"]
+    _, _, glb = load()
+    path = os.path.join(_LIDAR, "train", "predict.py")
+    with open(path) as f:
+        lines = f.readlines()
+    start = next(i for i, ln in enumerate(lines) if ln.startswith("def back_project_2D_2_3D("))
+    end = next(i for i in range(start + 1, len(lines)) if lines[i].startswith(("def ", "class ")))
+    import math
+    import numpy as np
+    ns = {"np": np, "sin": math.sin, "cos": math.cos, "X_MIN": glb.X_MIN, "RES_RAD": glb.RES_RAD,
+          "LIDAR_MIN_HEIGHT": glb.LIDAR_MIN_HEIGHT}
+    exec(compile("".join(lines[start:end]), path, "exec"), ns)
+    _cache["bp"] = ns["back_project_2D_2_3D"]
+    return _cache["bp"]

@@ -447,3 +447,47 @@ extern "C" int sfpe_selftest_fastpath(sfpe_ctx* c, const float* d_xyzi, int64_t 
   CK(c, e);
   return SFPE_OK;
 }
+
+// ---- consumers of the range scan ----------------------------------------------
+
+extern "C" int sfpe_invariant_mask_update(sfpe_ctx* c, const void* d_ref, const void* d_frames, int32_t dtype,
+                                          int64_t n_frames, int64_t frame_stride, int64_t n_pix, int32_t pix_stride,
+                                          uint8_t* d_mask, void* stream) {
+  if (!c || n_frames < 0 || n_pix < 0 || pix_stride < 1 || frame_stride < 0) return SFPE_ERR_INVALID_ARG;
+  if (dtype != SFPE_F32 && dtype != SFPE_F64) return SFPE_ERR_INVALID_ARG;
+  if (n_frames > 0 && n_pix > 0 && (!d_ref || !d_frames || !d_mask)) return SFPE_ERR_INVALID_ARG;
+  const size_t esz = dtype == SFPE_F32 ? 4 : 8;
+  if (((uintptr_t)d_ref % esz) || ((uintptr_t)d_frames % esz)) return SFPE_ERR_INVALID_ARG;
+  CK(c, cudaSetDevice(c->device));
+  int sms = 0;
+  CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+  CK(c, launch_mask_update(d_ref, d_frames, dtype, n_frames, frame_stride, n_pix, pix_stride, d_mask, sms,
+                           (cudaStream_t)stream, &c->launches));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_roll_width(sfpe_ctx* c, const void* d_in, void* d_out, int64_t n_frames, int32_t height,
+                               int32_t width, int32_t pix_bytes, const int32_t* d_shift, void* stream) {
+  if (!c || n_frames < 0 || height < 0 || width < 0 || pix_bytes <= 0 || pix_bytes % 4) return SFPE_ERR_INVALID_ARG;
+  const long long total = (long long)n_frames * height * width;
+  if (total > 0 && (!d_in || !d_out || !d_shift || d_in == d_out)) return SFPE_ERR_INVALID_ARG;
+  if (((uintptr_t)d_in % 4) || ((uintptr_t)d_out % 16)) return SFPE_ERR_INVALID_ARG;
+  if ((long long)width * (pix_bytes / 4) > 0x7fffffffll) return SFPE_ERR_UNSUPPORTED;
+  CK(c, cudaSetDevice(c->device));
+  CK(c, launch_roll_width(d_in, d_out, n_frames, height, width, pix_bytes, d_shift, (cudaStream_t)stream, &c->launches));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_back_project(sfpe_ctx* c, double* d_centroids, double* d_bboxes, int64_t n, const void* d_distance,
+                                 const void* d_height, int32_t dtype, int64_t frame_stride, int32_t pix_stride,
+                                 int32_t height, int32_t width, double min_height, double x_min, double res_rad,
+                                 double* d_xyz, int32_t* d_status, void* stream) {
+  if (!c || n < 0 || height <= 0 || width <= 0 || pix_stride < 1 || frame_stride < 0) return SFPE_ERR_INVALID_ARG;
+  if (dtype != SFPE_F32 && dtype != SFPE_F64) return SFPE_ERR_INVALID_ARG;
+  if (n > 0 && (!d_centroids || !d_bboxes || !d_distance || !d_height || !d_xyz || !d_status)) return SFPE_ERR_INVALID_ARG;
+  if ((long long)height * width > 0x7fffffffll || n > 0x7fffffffll) return SFPE_ERR_UNSUPPORTED;
+  CK(c, cudaSetDevice(c->device));
+  CK(c, launch_back_project(d_centroids, d_bboxes, n, d_distance, d_height, dtype, frame_stride, pix_stride, height, width,
+                            min_height, x_min, res_rad, d_xyz, d_status, (cudaStream_t)stream, &c->launches));
+  return SFPE_OK;
+}

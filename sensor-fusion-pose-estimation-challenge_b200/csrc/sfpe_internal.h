@@ -55,6 +55,17 @@ cudaError_t launch_decode_pc2(const void* blob, long long n, int step, int ox, i
 cudaError_t launch_colormap(const void* img, int dtype, long long n, int cmap, int autoscale, double vmin, double vmax,
                             unsigned long long* mm, unsigned char* rgb, cudaStream_t st, long long* launches);
 
+// consumers of the range scan (invariant mask, roll augmentation, back-projection) -- sfpe_post.cu
+cudaError_t launch_mask_update(const void* ref, const void* frames, int dtype, long long n_frames, long long frame_stride,
+                               long long n_pix, int pix_stride, unsigned char* mask, int sm_count, cudaStream_t st,
+                               long long* launches);
+cudaError_t launch_roll_width(const void* in, void* out, long long n_frames, int height, int width, int pix_bytes,
+                              const int* shift, cudaStream_t st, long long* launches);
+cudaError_t launch_back_project(double* centroids, double* bboxes, long long n, const void* distance, const void* height,
+                                int dtype, long long frame_stride, int pix_stride, int H, int W, double min_height,
+                                double x_min, double res_rad, double* xyz, int* status, cudaStream_t st,
+                                long long* launches);
+
 // fused one-sweep-per-SM path -- sfpe_fused.cu
 struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]

@@ -1,0 +1,158 @@
+"""Consumers of the range scan, kept on the device.
+
+    back_project_2D_2_3D      train/predict.py:230-293      -> sfpe_back_project
+    InvariantMask.update      process/create_lidar_invariant_mask.py:44-62 -> sfpe_invariant_mask_update
+    roll_width                train/loader.py:47-50 (np.roll(image, rotate_by, axis=1)) -> sfpe_roll_width
+
+The torch-tensor entries work on device-resident range scans as the projector writes them
+(`(B, 32, 1801, 3)` float32, channels distance / height / intensity); the numpy entries keep the
+reference's signatures (host arrays in, host arrays out, centroids / boxes updated in place).
+There is no CPU path: every function goes through libsfpe.so.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib, _session
+from .process import globals as G
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _dtype_code(t):
+    torch = _torch()
+    if t.dtype == torch.float32:
+        return _lib.SFPE_F32
+    if t.dtype == torch.float64:
+        return _lib.SFPE_F64
+    raise TypeError("range images must be float32 or float64, got %s" % t.dtype)
+
+
+def _stream_ptr(stream):
+    torch = _torch()
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _projector(device):
+    pr = _session.projector(enable_bev=False)
+    if device is not None and device.index is not None and device.index != pr.device:
+        raise ValueError("tensors live on cuda:%d but the session projector is on cuda:%d (set SFPE_DEVICE)"
+                         % (device.index, pr.device))
+    return pr
+
+
+class InvariantMask:
+    """Static-pixel mask over a stream of range scans: a pixel stays 1 while it equals the reference frame in
+    every frame seen (create_lidar_invariant_mask.py:59-62).  `reference`: device tensor of one frame, any shape;
+    `update(frames)`: device tensor of shape (n,) + reference.shape."""
+
+    def __init__(self, reference, stream=None):
+        torch = _torch()
+        if not reference.is_cuda:
+            raise ValueError("reference must be a CUDA tensor")
+        self.reference = reference.contiguous()
+        self.mask = torch.ones(self.reference.shape, dtype=torch.uint8, device=reference.device)
+        self._pr = _projector(reference.device)
+        self._stream = stream
+
+    def update(self, frames):
+        ref = self.reference
+        if frames.shape[1:] != ref.shape or frames.dtype != ref.dtype or frames.device != ref.device:
+            raise ValueError("frames must be (n,)+%s %s on %s" % (tuple(ref.shape), ref.dtype, ref.device))
+        frames = frames.contiguous()
+        n_pix = ref.numel()
+        rc = self._pr.lib.sfpe_invariant_mask_update(
+            self._pr._ctx, C.c_void_p(ref.data_ptr()), C.c_void_p(frames.data_ptr()), _dtype_code(ref),
+            frames.shape[0], n_pix, n_pix, 1, C.c_void_p(self.mask.data_ptr()), _stream_ptr(self._stream))
+        _lib.check(rc, self._pr._ctx)
+        return self.mask
+
+
+def roll_width(images, rotate_by, out=None, stream=None):
+    """np.roll(image, rotate_by[f], axis=1) for every (height, width, channels) item of a device batch
+    (train/loader.py:47-50).  images: (B, H, W, C) or (B, H, W) tensor of a 4-byte-multiple pixel size;
+    rotate_by: int, sequence of B ints, or int32 device tensor.  Returns a new tensor (or `out`)."""
+    torch = _torch()
+    if not images.is_cuda or images.dim() not in (3, 4):
+        raise ValueError("images must be a CUDA tensor of shape (B,H,W) or (B,H,W,C)")
+    images = images.contiguous()
+    B, H, W = images.shape[:3]
+    pix_bytes = images.element_size() * (images.shape[3] if images.dim() == 4 else 1)
+    if torch.is_tensor(rotate_by):
+        shift = rotate_by.to(device=images.device, dtype=torch.int32).contiguous()
+    else:
+        shift = torch.as_tensor(np.broadcast_to(np.asarray(rotate_by, dtype=np.int64) % max(W, 1), (B,)).astype(np.int32),
+                                device=images.device)
+    if shift.numel() != B:
+        raise ValueError("need one shift per batch item")
+    if out is None:
+        out = torch.empty_like(images)
+    elif out.shape != images.shape or out.dtype != images.dtype or not out.is_contiguous() or out.data_ptr() == images.data_ptr():
+        raise ValueError("out must be a distinct contiguous tensor shaped like images")
+    pr = _projector(images.device)
+    rc = pr.lib.sfpe_roll_width(pr._ctx, C.c_void_p(images.data_ptr()), C.c_void_p(out.data_ptr()), B, H, W, pix_bytes,
+                                C.c_void_p(shift.data_ptr()), _stream_ptr(stream))
+    _lib.check(rc, pr._ctx)
+    return out
+
+
+def back_project_device(centroids, bboxes, range_scan=None, distance=None, height=None, stream=None):
+    """Device form of back_project_2D_2_3D.  centroids (B,2) / bboxes (B,4): float64 CUDA tensors, updated in
+    place.  Either `range_scan` (B,H,W,3) as the projector writes it (distance, height, intensity) or separate
+    `distance` / `height` (B,H,W) tensors.  Returns (xyz (B,4) float64, status (B,) int32) device tensors;
+    status 3 marks items whose centroid or box lies outside the image."""
+    torch = _torch()
+    if range_scan is not None:
+        rs = range_scan.contiguous()
+        B, H, W, Cn = rs.shape
+        d_ptr, h_ptr = rs.data_ptr(), rs.data_ptr() + rs.element_size()
+        frame_stride, pix_stride, code, dev = H * W * Cn, Cn, _dtype_code(rs), rs.device
+        keep = (rs,)
+    else:
+        distance, height = distance.contiguous(), height.contiguous()
+        if distance.shape != height.shape or distance.dtype != height.dtype:
+            raise ValueError("distance and height must match")
+        B, H, W = distance.shape
+        d_ptr, h_ptr = distance.data_ptr(), height.data_ptr()
+        frame_stride, pix_stride, code, dev = H * W, 1, _dtype_code(distance), distance.device
+        keep = (distance, height)
+    for t, cols in ((centroids, 2), (bboxes, 4)):
+        if t.dtype != torch.float64 or tuple(t.shape) != (B, cols) or not t.is_contiguous() or t.device != dev:
+            raise ValueError("centroids (B,2) and bboxes (B,4) must be contiguous float64 tensors on %s" % dev)
+    xyz = torch.empty((B, 4), dtype=torch.float64, device=dev)
+    status = torch.empty((B,), dtype=torch.int32, device=dev)
+    pr = _projector(dev)
+    rc = pr.lib.sfpe_back_project(
+        pr._ctx, C.c_void_p(centroids.data_ptr()), C.c_void_p(bboxes.data_ptr()), B, C.c_void_p(d_ptr), C.c_void_p(h_ptr),
+        code, frame_stride, pix_stride, H, W, float(G.LIDAR_MIN_HEIGHT), float(G.X_MIN), float(G.RES_RAD[1]),
+        C.c_void_p(xyz.data_ptr()), C.c_void_p(status.data_ptr()), _stream_ptr(stream))
+    _lib.check(rc, pr._ctx)
+    del keep
+    return xyz, status
+
+
+def back_project_2D_2_3D(centroids, bboxes, distance_data, height_data):
+    """Reference signature (train/predict.py:230): numpy arrays in, `xyz_coor` (B,4) out; `centroids` and
+    `bboxes` are updated in place.  An item whose centroid or box lies outside the image raises IndexError
+    (the reference indexes out of range, or silently wraps, there)."""
+    torch = _torch()
+    pr = _projector(None)
+    dev = torch.device("cuda", pr.device)
+    d = np.ascontiguousarray(distance_data)
+    h = np.ascontiguousarray(height_data)
+    if d.dtype not in (np.float32, np.float64):
+        d = d.astype(np.float64)
+    h = h.astype(d.dtype, copy=False)
+    cen = torch.as_tensor(np.ascontiguousarray(centroids, dtype=np.float64)).to(dev)
+    box = torch.as_tensor(np.ascontiguousarray(bboxes, dtype=np.float64)).to(dev)
+    xyz, status = back_project_device(cen, box, distance=torch.as_tensor(d).to(dev), height=torch.as_tensor(h).to(dev))
+    status = status.cpu().numpy()
+    if (status == 3).any():
+        raise IndexError("centroid or bounding box outside the image for item(s) %s" % np.nonzero(status == 3)[0].tolist())
+    centroids[...] = cen.cpu().numpy()
+    bboxes[...] = box.cpu().numpy()
+    return xyz.cpu().numpy()

@@ -91,3 +91,44 @@ def make_pointcloud2_blob(points_f32, beams=32):
     rec["x"], rec["y"], rec["z"], rec["intensity"] = points_f32[:, 0], points_f32[:, 1], points_f32[:, 2], points_f32[:, 3]
     rec["ring"] = np.arange(n) % beams
     return rec.view(np.uint8).reshape(-1)
+
+
+def make_back_project_case(n_items=12, seed=0, height=32, width=1801):
+    """Synthetic input of the back-projection (train/predict.py:230-293): per item a sparse (distance, height)
+    range image pair plus a cluster centroid [column, row] and its box [left, top, right, bottom].  Covers a
+    centroid on a valid pixel, on an invalid one (nearest valid pixel of the box wins, ties included), a box
+    with nothing valid, a box whose left edge is 0 (the reference skips the search) and the (0,0) centroid.
+    Returns float32 images (exactly representable in float64) and float64 centroids / boxes."""
+    rng = np.random.default_rng(1000 + seed)
+    dist = np.zeros((n_items, height, width), np.float32)
+    hgt = np.full((n_items, height, width), -2.0, np.float32)
+    cen = np.zeros((n_items, 2))
+    box = np.zeros((n_items, 4))
+    for i in range(n_items):
+        fill = (0.01, 0.05, 0.3)[i % 3]
+        hit = rng.random((height, width)) < fill
+        dist[i][hit] = rng.uniform(1.0, 60.0, hit.sum()).astype(np.float32)
+        hgt[i][hit] = rng.uniform(-2.6, 1.5, hit.sum()).astype(np.float32)     # some hits sit below the height floor
+        cx, cy = rng.uniform(40, width - 40), rng.uniform(0, height - 0.01)
+        half_w, half_h = rng.integers(1, 30), rng.integers(0, 6)
+        l, r = int(cx) - half_w, int(cx) + half_w
+        t, b = max(int(cy) - half_h, 0), min(int(cy) + half_h, height - 1)
+        kind = i % 6
+        if kind == 1:      # centroid on a valid pixel, fractional coordinates kept for theta
+            dist[i, int(cy), int(cx)] = 12.5
+            hgt[i, int(cy), int(cx)] = 0.25
+        elif kind == 2:    # nothing valid inside the box
+            dist[i, t:b + 1, l:r + 1] = 0
+        elif kind == 3:    # left edge 0: no search, centroid used as it is
+            l = 0
+        elif kind == 4:    # symmetric pair at equal distance: the first in row-major order wins
+            dist[i, t:b + 1, l:r + 1] = 0
+            for dx in (-1, 1):
+                dist[i, int(cy), int(cx) + dx] = 7.0 + dx
+                hgt[i, int(cy), int(cx) + dx] = 0.5
+        elif kind == 5 and i >= 6:
+            cx, cy = 0.0, 0.0
+            l, t, r, b = 0, 0, 5, 3
+        cen[i] = (cx, cy)
+        box[i] = (l, t, r, b)
+    return dist, hgt, cen, box

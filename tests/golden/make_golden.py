@@ -92,7 +92,19 @@ def raises_case(name, pts32):
     raise SystemExit("%s: reference did NOT raise" % name)
 
 
+def back_project_case(name, seed):
+    """Reference back_project_2D_2_3D (train/predict.py:230-293) on a synthetic case; inputs kept as float32."""
+    dist, hgt, cen, box = synth.make_back_project_case(seed=seed)
+    cen_out, box_out = cen.copy(), box.copy()
+    xyz = rl.back_project_fn()(cen_out, box_out, dist.astype(np.float64), hgt.astype(np.float64))
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, distance=dist, height=hgt, centroids=cen, bboxes=box, centroids_out=cen_out,
+                        bboxes_out=box_out, xyz=xyz)
+    print(name, len(cen), "items ->", os.path.getsize(path) // 1024, "KiB")
+
+
 def main():
+    back_project_case("back_project_seed0", 0)
     run_case("hdl32_seed0", synth.make_sweep("hdl32", seed=0))
     run_case("hdl32_seed1_shuffled_dropout", synth.make_sweep("hdl32", seed=1, shuffle=True, dropout=0.05))
     run_case("hdl64_seed2", synth.make_sweep("hdl64", seed=2), bev_res=((0.2, 0.2),))

@@ -1,0 +1,118 @@
+"""-m gpu: the consumers of the range scan through libsfpe.so vs the oracle."""
+import numpy as np
+import pytest
+
+from conftest import golden, load_pkg, load_sub
+from oracle import lidar_oracle as lo
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def post():
+    load_pkg()
+    return load_sub("post")
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    return torch
+
+
+def test_back_project_vs_reference_golden(post):
+    g = golden("back_project_seed0")
+    for dt in (np.float64, np.float32):
+        cen, box = g["centroids"].copy(), g["bboxes"].copy()
+        xyz = post.back_project_2D_2_3D(cen, box, g["distance"].astype(dt), g["height"].astype(dt))
+        assert np.array_equal(cen, g["centroids_out"]) and np.array_equal(box, g["bboxes_out"])   # pixel choice: exact
+        assert np.array_equal(xyz[:, 2:], g["xyz"][:, 2:])                                        # height, pad: exact
+        # x, y go through the device's fp64 cos/sin (<= 2 ulp) against libm's: 1e-13 relative
+        np.testing.assert_allclose(xyz[:, :2], g["xyz"][:, :2], rtol=1e-13, atol=1e-13)
+
+
+def test_back_project_device_on_projector_output(post, torch):
+    """Range scans as the projector writes them ((B,H,W,3) float32) feed the back-projection without a copy."""
+    synth = load_sub("synth")
+    dist, hgt, cen, box = synth.make_back_project_case(n_items=30, seed=3)
+    rs = np.zeros(dist.shape + (3,), np.float32)
+    rs[..., 0], rs[..., 1], rs[..., 2] = dist, hgt, 7.0
+    c_want, b_want = cen.copy(), box.copy()
+    want = lo.back_project(c_want, b_want, dist.astype(np.float64), hgt.astype(np.float64))
+    d_cen, d_box = torch.as_tensor(cen).cuda(), torch.as_tensor(box).cuda()
+    xyz, status = post.back_project_device(d_cen, d_box, range_scan=torch.as_tensor(rs).cuda())
+    assert np.array_equal(d_cen.cpu().numpy(), c_want) and np.array_equal(d_box.cpu().numpy(), b_want)
+    np.testing.assert_allclose(xyz.cpu().numpy(), want, rtol=1e-13, atol=1e-13)
+    st = status.cpu().numpy()
+    moved = (cen != c_want).any(axis=1)
+    zeroed = (b_want == 0).all(axis=1) & (box != 0).any(axis=1)
+    assert np.array_equal(st == 2, zeroed) and np.array_equal(st == 1, moved & ~zeroed) and not (st == 3).any()
+
+
+def test_back_project_flags_items_outside_the_image(post):
+    dist = np.ones((3, 32, 1801)); hgt = np.zeros((3, 32, 1801))
+    dist[1] = 0
+    cen = np.array([[5.0, 40.0], [10.0, 3.0], [12.0, 4.0]])          # row 40 is outside; box of item 1 too wide
+    box = np.array([[1.0, 1, 9, 9], [1.0, 1, 1801, 5], [1.0, 1, 30, 5]])
+    with pytest.raises(IndexError):
+        post.back_project_2D_2_3D(cen, box, dist, hgt)
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+def test_invariant_mask_matches_numpy(post, torch, dtype):
+    rng = np.random.default_rng(5)
+    shape = (32, 1801, 3)
+    ref = rng.integers(0, 4, shape).astype(dtype)
+    ref[0, 0, 0] = np.nan
+    frames = np.repeat(ref[None], 37, axis=0)
+    flips = rng.random(frames.shape) < 0.01
+    frames[flips] += 1
+    frames[:, 3, 7, 1] = ref[3, 7, 1]                # a pixel that stays
+    want = np.ones(shape, dtype=bool)
+    for f in frames:
+        lo.invariant_mask_update(want, ref, f)
+    im = post.InvariantMask(torch.as_tensor(ref).cuda())
+    im.update(torch.as_tensor(frames[:20]).cuda())
+    got = im.update(torch.as_tensor(frames[20:]).cuda()).cpu().numpy().astype(bool)
+    assert np.array_equal(got, want)
+    assert not got[0, 0, 0] and got[3, 7, 1] and 0 < got.sum() < got.size
+
+
+def test_invariant_mask_single_channel_stride(post, torch):
+    """pix_stride 3: one channel of an HWC frame (the reference keeps one mask per channel)."""
+    import ctypes as C
+    rng = np.random.default_rng(6)
+    ref = rng.integers(0, 3, (32, 1801, 3)).astype(np.float32)
+    frames = np.repeat(ref[None], 9, axis=0)
+    frames[rng.random(frames.shape) < 0.05] += 1
+    want = (frames[..., 1] == ref[..., 1]).all(axis=0)
+    d_ref, d_fr = torch.as_tensor(ref).cuda(), torch.as_tensor(frames).cuda()
+    mask = torch.ones((32, 1801), dtype=torch.uint8, device="cuda")
+    pr = load_sub("_session").projector(enable_bev=False)
+    rc = pr.lib.sfpe_invariant_mask_update(pr._ctx, C.c_void_p(d_ref.data_ptr() + 4), C.c_void_p(d_fr.data_ptr() + 4), 0,
+                                           9, ref.size, 32 * 1801, 3, C.c_void_p(mask.data_ptr()), None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(mask.cpu().numpy().astype(bool), want)
+
+
+@pytest.mark.parametrize("shape", [(5, 32, 1801, 3), (3, 32, 1801), (4, 7, 13, 5), (2, 1, 1, 1)])
+def test_roll_width_matches_numpy(post, torch, shape):
+    rng = np.random.default_rng(8)
+    img = rng.standard_normal(shape).astype(np.float32)
+    shifts = rng.integers(0, shape[2], shape[0])
+    shifts[0] = 0
+    got = post.roll_width(torch.as_tensor(img).cuda(), shifts).cpu().numpy()
+    for f in range(shape[0]):
+        assert np.array_equal(got[f], lo.roll_width(img[f], int(shifts[f])))
+    neg = post.roll_width(torch.as_tensor(img).cuda(), -3 - 2 * shape[2]).cpu().numpy()     # any integer, like np.roll
+    assert np.array_equal(neg[-1], lo.roll_width(img[-1], -3 - 2 * shape[2]))
+
+
+def test_roll_width_labels_float64(post, torch):
+    """Labels roll with the image (loader.py:47-49): (H, W, label_dim) float64 works the same way."""
+    rng = np.random.default_rng(9)
+    lab = rng.standard_normal((3, 32, 1801, 2))
+    got = post.roll_width(torch.as_tensor(lab).cuda(), [1, 900, 1800]).cpu().numpy()
+    for f, s in enumerate([1, 900, 1800]):
+        assert np.array_equal(got[f], np.roll(lab[f], s, axis=1))

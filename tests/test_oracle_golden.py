@@ -99,3 +99,38 @@ def test_extension_definition_hand_case():
     c2 = (118 - 58, 118 - 60)
     assert h[0][c2] == -1.0 and h[1][c2] == 0.2 and it[c2] == 50.0
     assert (h[0] == -1.0).sum() == 119 * 119 - 1 and (it != 0).sum() == 2
+
+
+def test_back_project_matches_reference_golden():
+    """oracle.back_project vs outputs of the reference's own back_project_2D_2_3D (train/predict.py:230-293)."""
+    g = golden("back_project_seed0")
+    cen, box = g["centroids"].copy(), g["bboxes"].copy()
+    xyz = lo.back_project(cen, box, g["distance"].astype(np.float64), g["height"].astype(np.float64))
+    assert np.array_equal(xyz, g["xyz"])
+    assert np.array_equal(cen, g["centroids_out"]) and np.array_equal(box, g["bboxes_out"])
+    moved = (g["centroids"] != g["centroids_out"]).any(axis=1)
+    zeroed = (g["bboxes_out"] == 0).all(axis=1)
+    assert moved.sum() >= 4 and zeroed.sum() >= 2 and (~moved).sum() >= 3     # the fixture exercises every branch
+
+
+@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+def test_back_project_equals_live_reference(synth):
+    dist, hgt, cen, box = synth.make_back_project_case(n_items=18, seed=7)
+    c1, b1, c2, b2 = cen.copy(), box.copy(), cen.copy(), box.copy()
+    want = rl.back_project_fn()(c1, b1, dist.astype(np.float64), hgt.astype(np.float64))
+    got = lo.back_project(c2, b2, dist.astype(np.float64), hgt.astype(np.float64))
+    assert np.array_equal(want, got) and np.array_equal(c1, c2) and np.array_equal(b1, b2)
+
+
+def test_invariant_mask_and_roll_definitions():
+    """create_lidar_invariant_mask.py:59-62 and loader.py:47-50 are two numpy calls each; pin the restatement
+    on a hand case (a NaN never matches, the mask never comes back)."""
+    ref = np.array([1.0, 2.0, np.nan, 4.0])
+    mask = np.ones(4, dtype=bool)
+    lo.invariant_mask_update(mask, ref, np.array([1.0, 2.5, np.nan, 4.0]))
+    assert mask.tolist() == [True, False, False, True]
+    lo.invariant_mask_update(mask, ref, np.array([0.0, 2.0, 3.0, 4.0]))
+    assert mask.tolist() == [False, False, False, True]
+    img = np.arange(2 * 5 * 3).reshape(2, 5, 3)
+    out = lo.roll_width(img, 2)
+    assert np.array_equal(out[:, 2], img[:, 0]) and np.array_equal(out[:, 0], img[:, 3])
