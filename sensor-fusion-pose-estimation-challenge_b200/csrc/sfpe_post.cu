@@ -54,40 +54,52 @@ __global__ void __launch_bounds__(128) k_mask_update(const T* __restrict__ ref, 
 }
 
 // ---- roll along the width -----------------------------------------------------------------------------
-// Rows are row_words 32-bit words; out_row[(j + shift*pix_words) mod row_words] = in_row[j].  A thread writes four
-// consecutive output words of the flattened [frame][row][word] array (one 16-byte store) from four scalar loads.
-__global__ void __launch_bounds__(256) k_roll_width(const unsigned* __restrict__ in, unsigned* __restrict__ out,
-                                                    long long total_words, unsigned row_words, unsigned rows_per_frame,
-                                                    unsigned pix_words, unsigned width, const int* __restrict__ shift) {
-  const long long o = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (o >= total_words) return;
-  long long row = o / row_words;
-  unsigned col = (unsigned)(o - row * row_words);
-  unsigned v[4];
-  long long cached_frame = -1;
-  unsigned sw = 0;
+// Rows are row_words 32-bit words; out_row[(j + shift*pix_words) mod row_words] = in_row[j].  A CTA moves
+// ROLL_WORDS consecutive words of the flattened [frame][row][word] array; thread t owns words t, t+256, ...:
+// every warp load and store is one contiguous 128-byte request, eight loads are in flight per thread, and
+// the (row, column, frame) of a word is found by one division per thread and carried forward after that.
+constexpr int ROLL_THREADS = 256, ROLL_PER_THREAD = 8, ROLL_WORDS = ROLL_THREADS * ROLL_PER_THREAD;
+
+__device__ __forceinline__ unsigned roll_shift_words(const int* __restrict__ shift, long long frame, unsigned width,
+                                                     unsigned pix_words) {
+  int s = __ldg(shift + frame) % (int)width;   // np.roll takes any integer shift
+  if (s < 0) s += (int)width;
+  return (unsigned)s * pix_words;
+}
+
+__global__ void __launch_bounds__(ROLL_THREADS) k_roll_width(const unsigned* __restrict__ in, unsigned* __restrict__ out,
+                                                             long long total_words, unsigned row_words,
+                                                             unsigned rows_per_frame, unsigned pix_words, unsigned width,
+                                                             const int* __restrict__ shift) {
+  long long j = (long long)blockIdx.x * ROLL_WORDS + threadIdx.x;
+  if (j >= total_words) return;
+  long long row;
+  if (total_words <= 0xffffffffll) row = (unsigned)j / row_words; else row = j / row_words;
+  unsigned col = (unsigned)(j - row * row_words);
+  long long frame = total_words <= 0xffffffffll ? (long long)((unsigned)row / rows_per_frame) : row / rows_per_frame;
+  unsigned rif = (unsigned)(row - frame * rows_per_frame);
+  long long rowbase = row * row_words;
+  unsigned sw = roll_shift_words(shift, frame, width, pix_words);
+  unsigned v[ROLL_PER_THREAD];
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
-    if (o + u < total_words) {
-      const long long frame = row / rows_per_frame;
-      if (frame != cached_frame) {
-        int s = __ldg(shift + frame) % (int)width;   // np.roll takes any integer shift
-        if (s < 0) s += (int)width;
-        sw = (unsigned)s * pix_words;
-        cached_frame = frame;
-      }
+  for (int u = 0; u < ROLL_PER_THREAD; ++u) {
+    if (j + (long long)u * ROLL_THREADS < total_words) {
       const unsigned src = col >= sw ? col - sw : col + row_words - sw;
-      v[u] = __ldcs(in + row * row_words + src);
-      if (++col == row_words) { col = 0; ++row; }
-    } else {
-      v[u] = 0;
+      v[u] = __ldcs(in + rowbase + src);
+      col += ROLL_THREADS;
+      while (col >= row_words && j + (long long)(u + 1) * ROLL_THREADS < total_words) {
+        col -= row_words;
+        rowbase += row_words;
+        if (++rif == rows_per_frame) {
+          rif = 0;
+          sw = roll_shift_words(shift, ++frame, width, pix_words);
+        }
+      }
     }
   }
-  if (o + 3 < total_words) {
-    __stcs(reinterpret_cast<uint4*>(out + o), make_uint4(v[0], v[1], v[2], v[3]));
-  } else {
-    for (int u = 0; u < 4 && o + u < total_words; ++u) out[o + u] = v[u];
-  }
+#pragma unroll
+  for (int u = 0; u < ROLL_PER_THREAD; ++u)
+    if (j + (long long)u * ROLL_THREADS < total_words) __stcs(out + j + (long long)u * ROLL_THREADS, v[u]);
 }
 
 // ---- back-projection of cluster centroids ---------------------------------------------------------------
@@ -206,9 +218,9 @@ cudaError_t launch_roll_width(const void* in, void* out, long long n_frames, int
   const unsigned pix_words = (unsigned)pix_bytes / 4, row_words = pix_words * (unsigned)width;
   const long long total = n_frames * height * (long long)row_words;
   if (total <= 0) return cudaSuccess;
-  const long long blocks = (total / 4 + 256) / 256;
-  k_roll_width<<<(unsigned)blocks, 256, 0, st>>>((const unsigned*)in, (unsigned*)out, total, row_words, (unsigned)height,
-                                                 pix_words, (unsigned)width, shift);
+  const long long blocks = (total + ROLL_WORDS - 1) / ROLL_WORDS;
+  k_roll_width<<<(unsigned)blocks, ROLL_THREADS, 0, st>>>((const unsigned*)in, (unsigned*)out, total, row_words,
+                                                          (unsigned)height, pix_words, (unsigned)width, shift);
   ++*launches;
   return cudaGetLastError();
 }
