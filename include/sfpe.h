@@ -19,6 +19,7 @@
  *   sfpe_invariant_mask_update  process/create_lidar_invariant_mask.py:44-62
  *   sfpe_roll_width           train/loader.py:31-57 (data_random_rotate's np.roll)
  *   sfpe_back_project         train/predict.py:230-293 (back_project_2D_2_3D)
+ *   sfpe_find_bbox_3d         train/predict.py:94-199 (find_bbox_3d, is_far)
  *   sfpe_params defaults      process/globals.py:3-13 (RES, VFOV, LIDAR_MIN_HEIGHT, ...)
  *
  * Conventions: every function returns 0 (SFPE_OK) or a negative sfpe_status; nothing throws
@@ -209,6 +210,25 @@ SFPE_API int sfpe_back_project(sfpe_ctx* ctx, double* d_centroids, double* d_bbo
                       const void* d_distance, const void* d_height, int32_t dtype, int64_t frame_stride,
                       int32_t pix_stride, int32_t height, int32_t width, double min_height, double x_min,
                       double res_rad, double* d_xyz, int32_t* d_status, void* stream);
+
+/* Per-pixel box decode (train/predict.py:94-199, find_bbox_3d, with is_far :83-92).  Per item i:
+ * d_pred is the network output [height*width][26] (background p, car p, 8 corners x 3 in the pixel's
+ * rotated frame; `pred_dtype`); every pixel of the window [left-100, right+100) x [top-2, bottom+2)
+ * (d_bbox2d[i] = left, top, right, bottom) whose column holds a positive (p >= 0.5) pixel anywhere and
+ * whose row holds one anywhere is decoded to 8 corners (rot_z(theta) rot_y(phi) c' + p, fp64); sets
+ * with a corner further than (9,3,3) m from d_centroid3d[i] are dropped; the sets with the most
+ * neighbours (0 < Frobenius distance < 5 m) are averaged in window order -> d_out_box[i] (8x3);
+ * d_out_pred[i] = x, y, z (mean corner), yaw, length, width, height.  d_n_boxes[i] = sets kept
+ * (0: d_out_pred = 0 and no box, the reference's `None`; -1: more than `cap` sets, nothing written).
+ * Scratch: d_boxes [n][cap][24] float64, d_counts [n][cap] int32.  Images addressed like
+ * sfpe_back_project.  Decisions and sums follow the reference's order; the trigonometry and the
+ * 3x3 products are the device's fp64 (test tolerance 1e-9 absolute on metres / radians). */
+SFPE_API int sfpe_find_bbox_3d(sfpe_ctx* ctx, const void* d_distance, const void* d_height, int32_t dtype,
+                      int64_t frame_stride, int32_t pix_stride, const void* d_pred, int32_t pred_dtype,
+                      int64_t n, int32_t height, int32_t width, const int32_t* d_bbox2d,
+                      const double* d_centroid3d, double x_min, double y_min, double res_rad_h,
+                      double res_rad_v, double* d_boxes, int32_t* d_counts, int64_t cap,
+                      double* d_out_pred, double* d_out_box, int32_t* d_n_boxes, void* stream);
 
 /* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
 SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);

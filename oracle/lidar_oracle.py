@@ -288,3 +288,66 @@ def back_project(centroids, bboxes, distance_data, height_data):
             xyz[i, 1] = -dist * sin(theta)                             # :286
             xyz[i, 2] = hgt                                            # :287
     return xyz
+
+
+MIN_PROB = 0.5          # train/predict.py:28
+MAX_BBX_DIST = 5.0      # train/predict.py:31
+FAR_DELTA = (9.0, 3.0, 3.0)   # train/predict.py:85
+
+
+def decode_boxes(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
+    """First half of find_bbox_3d (train/predict.py:94-135): the decoded corner sets (K,8,3), in the reference's
+    order (column-major over the window), that are not far from the centroid.  A window pixel takes part when
+    its column holds a positive pixel SOMEWHERE and its row holds one SOMEWHERE (:105), not only when it is
+    positive itself."""
+    from math import sin, cos
+    h, w = distance_img.shape
+    y3 = np.reshape(y_pred, (h, w, 26))                                         # :95
+    pos_rows, pos_cols = np.where(y3[:, :, 1] >= MIN_PROB)                      # :96
+    row_has, col_has = np.zeros(h, bool), np.zeros(w, bool)
+    row_has[pos_rows] = True
+    col_has[pos_cols] = True
+    (ulx, uly), (lrx, lry) = bbox_2d                                            # :99
+    c3 = np.asarray(centroid_3d, dtype=np.float64)
+    boxes = []
+    for x in range(max(ulx - 100, 0), min(lrx + 100, w)):                       # :103 (outside the image nothing matches)
+        if not col_has[x]:
+            continue
+        for y in range(max(uly - 2, 0), min(lry + 2, h)):                       # :104
+            if not row_has[y]:
+                continue
+            d, z = float(distance_img[y, x]), float(height_img[y, x])           # :108-109
+            theta, phi = (x + X_MIN) * RES_RAD[1], (y + Y_MIN) * RES_RAD[0]     # :110-111
+            p = np.array([d * cos(theta), -d * sin(theta), z])                  # :112-115
+            rot_z = np.array([[cos(theta), -sin(theta), 0.0], [sin(theta), cos(theta), 0.0], [0.0, 0.0, 1.0]])
+            rot_y = np.array([[cos(phi), 0.0, sin(phi)], [0.0, 1.0, 0.0], [-sin(phi), 0.0, cos(phi)]])
+            rot = np.matmul(rot_z, rot_y)                                       # :128
+            c = np.matmul(rot, np.reshape(y3[y, x, 2:], (8, 3)).transpose()).transpose() + p   # :116,129
+            if (np.abs(c - c3) <= np.array(FAR_DELTA)).all():                   # :83-92, :132
+                boxes.append(c)
+    return np.array(boxes).reshape(len(boxes), 8, 3)
+
+
+def find_bbox_3d(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
+    """train/predict.py:94-199.  Returns (pred[7] = x, y, z, yaw, length, width, height; candidate box (8,3) or None)."""
+    from math import atan2, cos, pi
+    boxes = decode_boxes(distance_img, height_img, y_pred, bbox_2d, centroid_3d)
+    if len(boxes) == 0:
+        return np.zeros(7), None                                                # :137-138
+    diff = boxes[:, None] - boxes[None]                                         # :146-151 all pairs
+    d = np.sqrt((diff * diff).sum(axis=(2, 3)))
+    counts = np.logical_and(d > 0, d < MAX_BBX_DIST).sum(axis=1)
+    cand = boxes[counts == counts.max()].mean(axis=0)                           # :159-164 ties: all of them
+    pred = np.zeros(7)
+    pred[:3] = np.mean(cand, 0)                                                 # :167
+    yaws, ls, ws, hs = [], [], [], []
+    for i in range(4):                                                          # :174-192
+        dx, dy = cand[i, 0] - cand[i + 4, 0], cand[i, 1] - cand[i + 4, 1]
+        yaw = atan2(dy, dx)
+        yaws.append(yaw)
+        ls.append(abs(dx / cos(yaw) if yaw != pi / 2.0 else dy))
+        dx, dy = cand[i, 0] - cand[i + 2, 0], cand[i, 1] - cand[i + 2, 1]
+        ws.append(abs(dy / cos(yaw) if yaw != pi / 2.0 else dx))
+        hs.append(abs(cand[i, 2] - cand[i + 1, 2]))
+    pred[3], pred[4], pred[5], pred[6] = np.mean(yaws), np.mean(ls), np.mean(ws), np.mean(hs)   # :194-197
+    return pred, cand

@@ -132,3 +132,31 @@ def back_project_fn():
     exec(compile("".join(lines[start:end]), path, "exec"), ns)
     _cache["bp"] = ns["back_project_2D_2_3D"]
     return _cache["bp"]
+
+
+def _predict_functions(names):
+    """Compile the named top-level functions of train/predict.py (and the module constants they read) from their
+    own source lines -- see back_project_fn for why the module cannot be imported whole."""
+    _, _, glb = load()
+    path = os.path.join(_LIDAR, "train", "predict.py")
+    with open(path) as f:
+        lines = f.readlines()
+    import math
+    import numpy as np
+    ns = {"np": np, "sin": math.sin, "cos": math.cos, "atan2": math.atan2, "pi": math.pi, "X_MIN": glb.X_MIN,
+          "Y_MIN": glb.Y_MIN, "RES_RAD": glb.RES_RAD, "LIDAR_MIN_HEIGHT": glb.LIDAR_MIN_HEIGHT}
+    for ln in lines:      # MIN_PROB, MIN_BBOX_AREA, MIN_HEAT, MAX_BBX_DIST (predict.py:28-31)
+        if ln.startswith(("MIN_PROB", "MIN_BBOX_AREA", "MIN_HEAT", "MAX_BBX_DIST")):
+            exec(ln, ns)
+    for name in names:
+        start = next(i for i, ln in enumerate(lines) if ln.startswith("def %s(" % name))
+        end = next(i for i in range(start + 1, len(lines)) if lines[i].startswith(("def ", "class ")))
+        exec(compile("\n" * start + "".join(lines[start:end]), path, "exec"), ns)
+    return ns
+
+
+def find_bbox_3d_fn():
+    """The reference's find_bbox_3d (train/predict.py:94-199) with its helper is_far (:83-92), unmodified."""
+    if "fb" not in _cache:
+        _cache["fb"] = _predict_functions(["is_far", "find_bbox_3d"])["find_bbox_3d"]
+    return _cache["fb"]

@@ -491,3 +491,23 @@ extern "C" int sfpe_back_project(sfpe_ctx* c, double* d_centroids, double* d_bbo
                             min_height, x_min, res_rad, d_xyz, d_status, (cudaStream_t)stream, &c->launches));
   return SFPE_OK;
 }
+
+extern "C" int sfpe_find_bbox_3d(sfpe_ctx* c, const void* d_distance, const void* d_height, int32_t dtype,
+                                 int64_t frame_stride, int32_t pix_stride, const void* d_pred, int32_t pred_dtype, int64_t n,
+                                 int32_t height, int32_t width, const int32_t* d_bbox2d, const double* d_centroid3d,
+                                 double x_min, double y_min, double res_rad_h, double res_rad_v, double* d_boxes,
+                                 int32_t* d_counts, int64_t cap, double* d_out_pred, double* d_out_box, int32_t* d_n_boxes,
+                                 void* stream) {
+  if (!c || n < 0 || height <= 0 || width <= 0 || pix_stride < 1 || frame_stride < 0 || cap < 0) return SFPE_ERR_INVALID_ARG;
+  if ((dtype != SFPE_F32 && dtype != SFPE_F64) || (pred_dtype != SFPE_F32 && pred_dtype != SFPE_F64)) return SFPE_ERR_INVALID_ARG;
+  if (n > 0 && (!d_distance || !d_height || !d_pred || !d_bbox2d || !d_centroid3d || !d_out_pred || !d_out_box || !d_n_boxes ||
+                (cap > 0 && (!d_boxes || !d_counts))))
+    return SFPE_ERR_INVALID_ARG;
+  if ((long long)height * width > 0x7fffffffll / 26 || n > 0x7fffffffll || (long long)width + height > 200 * 1024)
+    return SFPE_ERR_UNSUPPORTED;
+  CK(c, cudaSetDevice(c->device));
+  CK(c, launch_find_bbox_3d(d_distance, d_height, dtype, frame_stride, pix_stride, d_pred, pred_dtype, n, height, width,
+                            d_bbox2d, d_centroid3d, x_min, y_min, res_rad_h, res_rad_v, d_boxes, d_counts, cap, d_out_pred,
+                            d_out_box, d_n_boxes, (cudaStream_t)stream, &c->launches));
+  return SFPE_OK;
+}

@@ -66,6 +66,12 @@ cudaError_t launch_back_project(double* centroids, double* bboxes, long long n, 
                                 double x_min, double res_rad, double* xyz, int* status, cudaStream_t st,
                                 long long* launches);
 
+cudaError_t launch_find_bbox_3d(const void* distance, const void* height, int dtype, long long frame_stride, int pix_stride,
+                                const void* y_pred, int pred_dtype, long long n, int H, int W, const int* bbox2d,
+                                const double* centroid3d, double x_min, double y_min, double res_h, double res_v,
+                                double* boxes, int* counts, long long cap, double* out_pred, double* out_box, int* n_boxes,
+                                cudaStream_t st, long long* launches);
+
 // fused one-sweep-per-SM path -- sfpe_fused.cu
 struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]

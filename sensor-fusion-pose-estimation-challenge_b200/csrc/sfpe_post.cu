@@ -1,4 +1,5 @@
 // Consumers of the range scan that stay on the device:
+//   k_find_bbox_3d  train/predict.py:94-199               per-pixel decode of the 3-D box corners + neighbour vote
 //   k_mask_update   create_lidar_invariant_mask.py:44-62  mask &= (reference == frame), every frame
 //   k_roll_width    train/loader.py:31-57                 np.roll(image, rotate_by, axis=1) per batch item
 //   k_back_project  train/predict.py:230-293              nearest valid pixel to a cluster centroid, then
@@ -189,6 +190,173 @@ __global__ void __launch_bounds__(128) k_back_project(double* __restrict__ centr
   status[i] = st;
 }
 
+
+// ---- per-pixel box decode (train/predict.py:94-199, find_bbox_3d) -----------------------------------------
+// One CTA per item.  (A) which rows / columns of the image hold a positive pixel anywhere (the reference's
+// `img_x in pos[1] and img_y in pos[0]`); (B) walk the window column by column, decode the 8 corners of every
+// participating pixel in fp64, drop the sets with a corner far from the centroid, and compact the rest IN ORDER
+// into `boxes` (block-wide exclusive scan per 256 window pixels); (C) neighbour counts, all pairs;
+// (D) mean of the sets with the highest count, accumulated in index order like numpy's axis-0 reduction;
+// (E) one thread derives position, yaw and size.
+constexpr int BOX_THREADS = 256;
+
+template <typename T, typename TP>
+__global__ void __launch_bounds__(BOX_THREADS) k_find_bbox_3d(
+    const T* __restrict__ distance, const T* __restrict__ height, long long frame_stride, int pix_stride,
+    const TP* __restrict__ y_pred, int H, int W, const int* __restrict__ bbox2d, const double* __restrict__ centroid3d,
+    double x_min, double y_min, double res_h, double res_v, double* __restrict__ boxes_all, int* __restrict__ counts_all,
+    long long cap, double* __restrict__ out_pred, double* __restrict__ out_box, int* __restrict__ n_boxes) {
+  extern __shared__ unsigned char flags[];   // [W] column flags, then [H] row flags
+  __shared__ int s_warp[BOX_THREADS / 32];
+  __shared__ int s_base, s_max;
+  __shared__ double s_cand[24];
+  const long long item = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const T* dist = distance + item * frame_stride;
+  const T* hgt = height + item * frame_stride;
+  const TP* yp = y_pred + item * (long long)H * W * 26;
+  double* boxes = boxes_all + item * cap * 24;
+  int* counts = counts_all + item * cap;
+  unsigned char* colflag = flags;
+  unsigned char* rowflag = flags + W;
+  for (int k = tid; k < W + H; k += BOX_THREADS) flags[k] = 0;
+  if (tid == 0) { s_base = 0; s_max = 0; }
+  __syncthreads();
+  for (int p = tid; p < H * W; p += BOX_THREADS)
+    if ((double)yp[(long long)p * 26 + 1] >= 0.5) {   // MIN_PROB, predict.py:28,96
+      const int r = p / W;
+      colflag[p - r * W] = 1;
+      rowflag[r] = 1;
+    }
+  __syncthreads();
+  const int x0 = max(bbox2d[4 * item] - 100, 0), x1 = min(bbox2d[4 * item + 2] + 100, W);
+  const int y0 = max(bbox2d[4 * item + 1] - 2, 0), y1 = min(bbox2d[4 * item + 3] + 2, H);
+  const int wh = max(y1 - y0, 0), n_win = max(x1 - x0, 0) * wh;
+  const double c3x = centroid3d[3 * item], c3y = centroid3d[3 * item + 1], c3z = centroid3d[3 * item + 2];
+  bool overflow = false;
+  for (int w0 = 0; w0 < n_win; w0 += BOX_THREADS) {
+    const int k = w0 + tid;
+    bool keep = false;
+    double c[24];
+    if (k < n_win) {
+      const int wx = k / wh, x = x0 + wx, y = y0 + (k - wx * wh);
+      if (colflag[x] && rowflag[y]) {
+        const long long at = ((long long)y * W + x) * pix_stride;
+        const double d = (double)dist[at], z = (double)hgt[at];
+        const double theta = (x + x_min) * res_h, phi = (y + y_min) * res_v;
+        double st, ct, sp, cp;
+        sincos(theta, &st, &ct);
+        sincos(phi, &sp, &cp);
+        const double px = d * ct, py = -d * st;
+        // rot_z . rot_y (predict.py:119-128)
+        const double r00 = ct * cp, r01 = -st, r02 = ct * sp, r10 = st * cp, r11 = ct, r12 = st * sp, r20 = -sp, r22 = cp;
+        const TP* q = yp + ((long long)y * W + x) * 26 + 2;
+        keep = true;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const double a = (double)q[3 * j], b = (double)q[3 * j + 1], e = (double)q[3 * j + 2];
+          const double cx = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(r00, a), __dmul_rn(r01, b)), __dmul_rn(r02, e)), px);
+          const double cy = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(r10, a), __dmul_rn(r11, b)), __dmul_rn(r12, e)), py);
+          const double cz = __dadd_rn(__dadd_rn(__dmul_rn(r20, a), __dmul_rn(r22, e)), z);
+          c[3 * j] = cx; c[3 * j + 1] = cy; c[3 * j + 2] = cz;
+          // is_far (predict.py:83-92): delta = 9, 3, 3
+          if (cx > c3x + 9.0 || cx < c3x - 9.0 || cy > c3y + 3.0 || cy < c3y - 3.0 || cz > c3z + 3.0 || cz < c3z - 3.0) keep = false;
+        }
+      }
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp[wid] = __popc(bal);
+    __syncthreads();
+    int before = s_base;
+    for (int w = 0; w < wid; ++w) before += s_warp[w];
+    const int slot = before + __popc(bal & ((1u << lane) - 1));
+    if (keep) {
+      if (slot < cap) {
+#pragma unroll
+        for (int j = 0; j < 24; ++j) boxes[(long long)slot * 24 + j] = c[j];
+      } else {
+        overflow = true;
+      }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      int tot = 0;
+      for (int w = 0; w < BOX_THREADS / 32; ++w) tot += s_warp[w];
+      s_base += tot;
+    }
+    __syncthreads();
+  }
+  const int K = s_base;
+  if (__syncthreads_or(overflow) || K > cap) {
+    if (tid == 0) n_boxes[item] = -1;
+    return;
+  }
+  if (K == 0) {   // predict.py:137-138: zeros(7), None
+    if (tid < 7) out_pred[7 * item + tid] = 0.0;
+    if (tid < 24) out_box[24 * item + tid] = 0.0;
+    if (tid == 0) n_boxes[item] = 0;
+    return;
+  }
+  // (C) neighbour counts: 0 < ||c - c2|| < MAX_BBX_DIST (predict.py:146-151)
+  for (int i = tid; i < K; i += BOX_THREADS) {
+    double mine[24];
+#pragma unroll
+    for (int j = 0; j < 24; ++j) mine[j] = boxes[(long long)i * 24 + j];
+    int cnt = 0;
+    for (int o = 0; o < K; ++o) {
+      double ssq = 0.0;
+#pragma unroll
+      for (int j = 0; j < 24; ++j) {
+        const double df = mine[j] - boxes[(long long)o * 24 + j];
+        ssq = __dadd_rn(ssq, __dmul_rn(df, df));
+      }
+      const double dd = sqrt(ssq);
+      cnt += (dd > 0.0 && dd < 5.0) ? 1 : 0;
+    }
+    counts[i] = cnt;
+    atomicMax(&s_max, cnt);
+  }
+  __syncthreads();
+  // (D) mean over the sets with the highest count, summed in index order (predict.py:159-164)
+  if (tid < 24) {
+    const int mx = s_max;
+    double acc = 0.0;
+    int m = 0;
+    for (int i = 0; i < K; ++i)
+      if (counts[i] == mx) { acc = m ? acc + boxes[(long long)i * 24 + tid] : boxes[(long long)i * 24 + tid]; ++m; }
+    acc /= (double)m;
+    s_cand[tid] = acc;
+    out_box[24 * item + tid] = acc;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  // (E) predict.py:166-197
+  double* pr = out_pred + 7 * item;
+  for (int a = 0; a < 3; ++a) {
+    double acc = s_cand[a];
+    for (int j = 1; j < 8; ++j) acc += s_cand[3 * j + a];
+    pr[a] = acc / 8.0;
+  }
+  double yaw_s = 0.0, l_s = 0.0, w_s = 0.0, h_s = 0.0;
+  const double half_pi = 3.141592653589793 / 2.0;
+  for (int i = 0; i < 4; ++i) {
+    double dx = s_cand[3 * i] - s_cand[3 * (i + 4)], dy = s_cand[3 * i + 1] - s_cand[3 * (i + 4) + 1];
+    const double yaw = atan2(dy, dx);
+    const double cyaw = cos(yaw);
+    const double bl = yaw != half_pi ? dx / cyaw : dy;
+    dx = s_cand[3 * i] - s_cand[3 * (i + 2)];
+    dy = s_cand[3 * i + 1] - s_cand[3 * (i + 2) + 1];
+    const double bw = yaw != half_pi ? dy / cyaw : dx;
+    const double bh = s_cand[3 * i + 2] - s_cand[3 * (i + 1) + 2];
+    yaw_s = i ? yaw_s + yaw : yaw;
+    l_s = i ? l_s + fabs(bl) : fabs(bl);
+    w_s = i ? w_s + fabs(bw) : fabs(bw);
+    h_s = i ? h_s + fabs(bh) : fabs(bh);
+  }
+  pr[3] = yaw_s / 4.0; pr[4] = l_s / 4.0; pr[5] = w_s / 4.0; pr[6] = h_s / 4.0;
+  n_boxes[item] = K;
+}
+
 }  // namespace
 
 cudaError_t launch_mask_update(const void* ref, const void* frames, int dtype, long long n_frames, long long frame_stride,
@@ -236,6 +404,26 @@ cudaError_t launch_back_project(double* centroids, double* bboxes, long long n, 
   else
     k_back_project<double><<<(unsigned)n, 128, 0, st>>>(centroids, bboxes, (const double*)distance, (const double*)height,
                                                         frame_stride, pix_stride, H, W, min_height, x_min, res_rad, xyz, status);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_find_bbox_3d(const void* distance, const void* height, int dtype, long long frame_stride, int pix_stride,
+                                const void* y_pred, int pred_dtype, long long n, int H, int W, const int* bbox2d,
+                                const double* centroid3d, double x_min, double y_min, double res_h, double res_v,
+                                double* boxes, int* counts, long long cap, double* out_pred, double* out_box, int* n_boxes,
+                                cudaStream_t st, long long* launches) {
+  if (n <= 0) return cudaSuccess;
+  const size_t smem = (size_t)W + H;
+#define SFPE_BOX_LAUNCH(T, TP)                                                                                          \
+  k_find_bbox_3d<T, TP><<<(unsigned)n, BOX_THREADS, smem, st>>>((const T*)distance, (const T*)height, frame_stride,       \
+      pix_stride, (const TP*)y_pred, H, W, bbox2d, centroid3d, x_min, y_min, res_h, res_v, boxes, counts, cap, out_pred,  \
+      out_box, n_boxes)
+  if (dtype == SFPE_F32 && pred_dtype == SFPE_F32) SFPE_BOX_LAUNCH(float, float);
+  else if (dtype == SFPE_F32) SFPE_BOX_LAUNCH(float, double);
+  else if (pred_dtype == SFPE_F32) SFPE_BOX_LAUNCH(double, float);
+  else SFPE_BOX_LAUNCH(double, double);
+#undef SFPE_BOX_LAUNCH
   ++*launches;
   return cudaGetLastError();
 }

@@ -2,6 +2,7 @@
 
     back_project_2D_2_3D      train/predict.py:230-293      -> sfpe_back_project
     InvariantMask.update      process/create_lidar_invariant_mask.py:44-62 -> sfpe_invariant_mask_update
+    find_bbox_3d              train/predict.py:94-199 (+ is_far :83-92) -> sfpe_find_bbox_3d
     roll_width                train/loader.py:47-50 (np.roll(image, rotate_by, axis=1)) -> sfpe_roll_width
 
 The torch-tensor entries work on device-resident range scans as the projector writes them
@@ -156,3 +157,73 @@ def back_project_2D_2_3D(centroids, bboxes, distance_data, height_data):
     centroids[...] = cen.cpu().numpy()
     bboxes[...] = box.cpu().numpy()
     return xyz.cpu().numpy()
+
+
+def find_bbox_3d_device(y_pred, bbox_2d, centroid_3d, range_scan=None, distance=None, height=None, cap=None, stream=None):
+    """Device form of find_bbox_3d for a batch.  y_pred (B, H*W, 26) float32/float64 CUDA tensor; bbox_2d (B,4)
+    int32 [left, top, right, bottom]; centroid_3d (B,3) float64; images as in back_project_device.  Returns
+    (pred (B,7) float64, box (B,8,3) float64, n_boxes (B,) int32) device tensors; n_boxes 0 = the reference's
+    `(zeros(7), None)`."""
+    torch = _torch()
+    if range_scan is not None:
+        rs = range_scan.contiguous()
+        B, H, W, Cn = rs.shape
+        d_ptr, h_ptr = rs.data_ptr(), rs.data_ptr() + rs.element_size()
+        frame_stride, pix_stride, code, dev = H * W * Cn, Cn, _dtype_code(rs), rs.device
+    else:
+        distance, height = distance.contiguous(), height.contiguous()
+        B, H, W = distance.shape
+        d_ptr, h_ptr = distance.data_ptr(), height.data_ptr()
+        frame_stride, pix_stride, code, dev = H * W, 1, _dtype_code(distance), distance.device
+    y_pred = y_pred.contiguous()
+    if tuple(y_pred.shape) != (B, H * W, 26) or y_pred.device != dev:
+        raise ValueError("y_pred must be (B, H*W, 26) on %s" % dev)
+    bbox_2d = bbox_2d.to(device=dev, dtype=torch.int32).contiguous()
+    centroid_3d = centroid_3d.to(device=dev, dtype=torch.float64).contiguous()
+    if tuple(bbox_2d.shape) != (B, 4) or tuple(centroid_3d.shape) != (B, 3):
+        raise ValueError("bbox_2d must be (B,4) and centroid_3d (B,3)")
+    if cap is None:     # the largest window: nothing can overflow
+        bb = bbox_2d.cpu().numpy().astype(np.int64)
+        wx = np.clip(np.minimum(bb[:, 2] + 100, W) - np.maximum(bb[:, 0] - 100, 0), 0, None)
+        wy = np.clip(np.minimum(bb[:, 3] + 2, H) - np.maximum(bb[:, 1] - 2, 0), 0, None)
+        cap = int((wx * wy).max()) if B else 0
+    cap = max(int(cap), 1)
+    boxes = torch.empty((B, cap, 24), dtype=torch.float64, device=dev)
+    counts = torch.empty((B, cap), dtype=torch.int32, device=dev)
+    pred = torch.empty((B, 7), dtype=torch.float64, device=dev)
+    box = torch.empty((B, 8, 3), dtype=torch.float64, device=dev)
+    n_boxes = torch.empty((B,), dtype=torch.int32, device=dev)
+    pr = _projector(dev)
+    rc = pr.lib.sfpe_find_bbox_3d(
+        pr._ctx, C.c_void_p(d_ptr), C.c_void_p(h_ptr), code, frame_stride, pix_stride, C.c_void_p(y_pred.data_ptr()),
+        _dtype_code(y_pred), B, H, W, C.c_void_p(bbox_2d.data_ptr()), C.c_void_p(centroid_3d.data_ptr()),
+        float(G.X_MIN), float(G.Y_MIN), float(G.RES_RAD[1]), float(G.RES_RAD[0]), C.c_void_p(boxes.data_ptr()),
+        C.c_void_p(counts.data_ptr()), cap, C.c_void_p(pred.data_ptr()), C.c_void_p(box.data_ptr()),
+        C.c_void_p(n_boxes.data_ptr()), _stream_ptr(stream))
+    _lib.check(rc, pr._ctx)
+    torch.cuda.current_stream().synchronize() if stream is None else stream.synchronize()   # scratch is freed on return
+    return pred, box, n_boxes
+
+
+def find_bbox_3d(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
+    """Reference signature (train/predict.py:94): one frame, numpy in, `(pred[7], candidate_bbox (8,3) or None)` out."""
+    torch = _torch()
+    pr = _projector(None)
+    dev = torch.device("cuda", pr.device)
+    d = np.ascontiguousarray(distance_img)
+    if d.dtype not in (np.float32, np.float64):
+        d = d.astype(np.float64)
+    h = np.ascontiguousarray(height_img).astype(d.dtype, copy=False)
+    H, W = d.shape
+    y = np.ascontiguousarray(y_pred)
+    if y.dtype not in (np.float32, np.float64):
+        y = y.astype(np.float64)
+    y = y.reshape(1, H * W, 26)
+    (ulx, uly), (lrx, lry) = bbox_2d
+    pred, box, n = find_bbox_3d_device(
+        torch.as_tensor(y).to(dev), torch.tensor([[ulx, uly, lrx, lry]], dtype=torch.int32),
+        torch.tensor([[float(v) for v in centroid_3d[:3]]], dtype=torch.float64),
+        distance=torch.as_tensor(d[None]).to(dev), height=torch.as_tensor(h[None]).to(dev))
+    if int(n[0]) == 0:
+        return np.zeros(7), None
+    return pred[0].cpu().numpy(), box[0].cpu().numpy()

@@ -132,3 +132,53 @@ def make_back_project_case(n_items=12, seed=0, height=32, width=1801):
         cen[i] = (cx, cy)
         box[i] = (l, t, r, b)
     return dist, hgt, cen, box
+
+
+def make_bbox_decode_case(seed=0, height=32, width=1801, noise=0.35, strays=6):
+    """Synthetic input of the per-pixel box decode (train/predict.py:94-199, find_bbox_3d): an FCN output
+    `y_pred` (height*width, 26) float32 -- [p(background), p(car), 8 corners x 3 in the pixel's rotated frame] --
+    with one blob of positive pixels on a car, a few stray positives elsewhere (they widen the reference's
+    row / column membership test), the matching float32 distance / height images, the blob's 2-D box
+    ((left, top), (right, bottom)) and a 3-D centroid.  Regression noise makes the neighbour counts differ."""
+    rng = np.random.default_rng(2000 + seed)
+    res_v, res_h = 1.33 * np.pi / 180, 0.2 * np.pi / 180
+    x_min, y_min = -900.0, -30.67 / 1.33
+    cx0 = int(rng.integers(150, width - 150))
+    cy0 = int(rng.integers(8, height - 8))
+    d0 = float(rng.uniform(8.0, 30.0))
+    half_w, half_h = int(rng.integers(6, 16)), int(rng.integers(2, 4))
+    theta0 = (cx0 + x_min) * res_h
+    centre = np.array([(d0 + 1.0) * np.cos(theta0), -(d0 + 1.0) * np.sin(theta0), -0.6])
+    yaw = float(rng.uniform(-np.pi, np.pi))
+    l, w, h = 4.5, 1.8, 1.5
+    corners = np.zeros((8, 3))
+    for k in range(8):   # bit 2: front/back, bit 1: left/right, bit 0: top/bottom (predict.py:176-190)
+        sx, sy, sz = (1 if not k & 4 else -1), (1 if not k & 2 else -1), (1 if not k & 1 else -1)
+        bx, by = sx * l / 2, sy * w / 2
+        corners[k] = centre + (bx * np.cos(yaw) - by * np.sin(yaw), bx * np.sin(yaw) + by * np.cos(yaw), sz * h / 2)
+    dist = rng.uniform(2.0, 60.0, (height, width)).astype(np.float32)
+    hgt = rng.uniform(-1.9, 1.0, (height, width)).astype(np.float32)
+    y = np.zeros((height, width, 26), np.float32)
+    y[..., 1] = rng.uniform(0.0, 0.45, (height, width))
+    positives = [(cy, cx) for cy in range(cy0 - half_h, cy0 + half_h + 1) for cx in range(cx0 - half_w, cx0 + half_w + 1)
+                 if rng.random() < 0.85]
+    for _ in range(strays):
+        positives.append((int(rng.integers(0, height)), int(rng.integers(0, width))))
+        positives.append((int(rng.integers(max(cy0 - 4, 0), min(cy0 + 4, height))), int(rng.integers(max(cx0 - 90, 0), min(cx0 + 90, width)))))
+    for cy, cx in positives:
+        y[cy, cx, 1] = rng.uniform(0.5, 1.0)
+        dist[cy, cx] = d0 + rng.uniform(-0.5, 0.5)
+        hgt[cy, cx] = rng.uniform(-1.2, 0.2)
+    # regression targets for every pixel of the neighbourhood (the reference decodes non-positive pixels too when
+    # their row and column each hold a positive somewhere): corners in the pixel's frame, plus noise
+    for cy in range(max(cy0 - half_h - 6, 0), min(cy0 + half_h + 7, height)):
+        for cx in range(max(cx0 - half_w - 110, 0), min(cx0 + half_w + 111, width)):
+            th, ph = (cx + x_min) * res_h, (cy + y_min) * res_v
+            p = np.array([dist[cy, cx] * np.cos(th), -dist[cy, cx] * np.sin(th), hgt[cy, cx]], dtype=np.float64)
+            rz = np.array([[np.cos(th), -np.sin(th), 0], [np.sin(th), np.cos(th), 0], [0, 0, 1]])
+            ry = np.array([[np.cos(ph), 0, np.sin(ph)], [0, 1, 0], [-np.sin(ph), 0, np.cos(ph)]])
+            rel = (corners + rng.normal(0, noise, (8, 3)) - p) @ (rz @ ry)      # rot^T (c - p), row-vector form
+            y[cy, cx, 2:] = rel.reshape(24)
+    bbox_2d = ((cx0 - half_w, cy0 - half_h), (cx0 + half_w, cy0 + half_h))
+    centroid_3d = centre + rng.normal(0, 0.3, 3)
+    return dist, hgt, y.reshape(height * width, 26), bbox_2d, centroid_3d

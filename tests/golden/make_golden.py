@@ -103,8 +103,23 @@ def back_project_case(name, seed):
     print(name, len(cen), "items ->", os.path.getsize(path) // 1024, "KiB")
 
 
+def bbox_decode_case(name, seeds):
+    """Reference find_bbox_3d (train/predict.py:94-199) on synthetic cases.  Only the window neighbourhood of
+    y_pred is kept (float16-free: float32 as generated); the test rebuilds the full array around it."""
+    out = {}
+    for k, seed in enumerate(seeds):
+        dist, hgt, y, bb, c3 = synth.make_bbox_decode_case(seed=seed)
+        pred, box = rl.find_bbox_3d_fn()(dist.astype(np.float64), hgt.astype(np.float64), y, bb, c3)
+        out.update({"seed%d" % k: seed, "bbox%d" % k: np.array(bb), "centroid%d" % k: c3, "pred%d" % k: pred,
+                    "box%d" % k: np.zeros((8, 3)) if box is None else box, "none%d" % k: box is None})
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, n=len(seeds), **out)
+    print(name, len(seeds), "cases ->", os.path.getsize(path) // 1024, "KiB")
+
+
 def main():
     back_project_case("back_project_seed0", 0)
+    bbox_decode_case("bbox_decode", [0, 1, 2, 3])
     run_case("hdl32_seed0", synth.make_sweep("hdl32", seed=0))
     run_case("hdl32_seed1_shuffled_dropout", synth.make_sweep("hdl32", seed=1, shuffle=True, dropout=0.05))
     run_case("hdl64_seed2", synth.make_sweep("hdl64", seed=2), bev_res=((0.2, 0.2),))

@@ -116,3 +116,46 @@ def test_roll_width_labels_float64(post, torch):
     got = post.roll_width(torch.as_tensor(lab).cuda(), [1, 900, 1800]).cpu().numpy()
     for f, s in enumerate([1, 900, 1800]):
         assert np.array_equal(got[f], np.roll(lab[f], s, axis=1))
+
+
+def _bbox_cases():
+    synth = load_sub("synth")
+    g = golden("bbox_decode")
+    for k in range(int(g["n"])):
+        yield synth.make_bbox_decode_case(seed=int(g["seed%d" % k])) + (g["pred%d" % k], g["box%d" % k])
+
+
+def test_find_bbox_3d_vs_reference_golden(post):
+    """Decisions (which corner sets take part, neighbour counts, ties) follow the reference; the fp64 trigonometry
+    and 3x3 products are the device's: 1e-9 absolute on metres / radians."""
+    for dist, hgt, y, bb, c3, pred, box in _bbox_cases():
+        for dt in (np.float64, np.float32):
+            got_pred, got_box = post.find_bbox_3d(dist.astype(dt), hgt.astype(dt), y, bb, c3)
+            np.testing.assert_allclose(got_box, box, rtol=0, atol=1e-9)
+            np.testing.assert_allclose(got_pred, pred, rtol=0, atol=1e-9)
+
+
+def test_find_bbox_3d_none_when_everything_is_far(post):
+    dist, hgt, y, bb, c3 = load_sub("synth").make_bbox_decode_case(seed=5)
+    pred, box = post.find_bbox_3d(dist, hgt, y, bb, c3 + 100.0)
+    assert box is None and pred.shape == (7,) and not pred.any()
+
+
+def test_find_bbox_3d_device_batch_and_overflow(post, torch):
+    synth = load_sub("synth")
+    cases = [synth.make_bbox_decode_case(seed=s, strays=st) for s, st in ((21, 0), (22, 6), (23, 20))]
+    scan = np.zeros((3, 32, 1801, 3), np.float32)
+    for i, c in enumerate(cases):
+        scan[i, ..., 0], scan[i, ..., 1] = c[0], c[1]
+    y = torch.as_tensor(np.stack([c[2] for c in cases])).cuda()
+    bb = torch.tensor([[c[3][0][0], c[3][0][1], c[3][1][0], c[3][1][1]] for c in cases], dtype=torch.int32)
+    c3 = torch.as_tensor(np.stack([c[4] for c in cases]))
+    pred, box, n = post.find_bbox_3d_device(y, bb, c3, range_scan=torch.as_tensor(scan).cuda())
+    for i, c in enumerate(cases):
+        d64, h64 = c[0].astype(np.float64), c[1].astype(np.float64)
+        want_pred, want_box = lo.find_bbox_3d(d64, h64, c[2], c[3], c[4])
+        assert int(n[i]) == len(lo.decode_boxes(d64, h64, c[2], c[3], c[4]))          # same sets kept
+        np.testing.assert_allclose(box[i].cpu().numpy(), want_box, rtol=0, atol=1e-9)
+        np.testing.assert_allclose(pred[i].cpu().numpy(), want_pred, rtol=0, atol=1e-9)
+    _, _, n_small = post.find_bbox_3d_device(y, bb, c3, range_scan=torch.as_tensor(scan).cuda(), cap=8)
+    assert (n_small.cpu().numpy() == -1).all()                                          # scratch too small: flagged

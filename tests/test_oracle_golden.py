@@ -134,3 +134,32 @@ def test_invariant_mask_and_roll_definitions():
     img = np.arange(2 * 5 * 3).reshape(2, 5, 3)
     out = lo.roll_width(img, 2)
     assert np.array_equal(out[:, 2], img[:, 0]) and np.array_equal(out[:, 0], img[:, 3])
+
+
+def _bbox_cases(synth):
+    g = golden("bbox_decode")
+    for k in range(int(g["n"])):
+        dist, hgt, y, bb, c3 = synth.make_bbox_decode_case(seed=int(g["seed%d" % k]))
+        assert np.array_equal(np.array(bb), g["bbox%d" % k]) and np.array_equal(c3, g["centroid%d" % k])   # same inputs
+        yield dist, hgt, y, bb, c3, g["pred%d" % k], (None if bool(g["none%d" % k]) else g["box%d" % k])
+
+
+def test_find_bbox_3d_matches_reference_golden(synth):
+    """oracle.find_bbox_3d vs outputs of the reference's own find_bbox_3d (train/predict.py:94-199)."""
+    for dist, hgt, y, bb, c3, pred, box in _bbox_cases(synth):
+        got_pred, got_box = lo.find_bbox_3d(dist.astype(np.float64), hgt.astype(np.float64), y, bb, c3)
+        assert np.array_equal(got_pred, pred) and np.array_equal(got_box, box)
+        assert len(lo.decode_boxes(dist.astype(np.float64), hgt.astype(np.float64), y, bb, c3)) > 100
+
+
+@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+def test_find_bbox_3d_equals_live_reference(synth):
+    for seed, strays in ((11, 0), (12, 12)):
+        dist, hgt, y, bb, c3 = synth.make_bbox_decode_case(seed=seed, strays=strays)
+        d64, h64 = dist.astype(np.float64), hgt.astype(np.float64)
+        want = rl.find_bbox_3d_fn()(d64, h64, y, bb, c3)
+        got = lo.find_bbox_3d(d64, h64, y, bb, c3)
+        assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1])
+    far = rl.find_bbox_3d_fn()(d64, h64, y, bb, c3 + 100.0)          # every set is far: zeros(7), None
+    assert far[1] is None and not far[0].any()
+    assert lo.find_bbox_3d(d64, h64, y, bb, c3 + 100.0)[1] is None
