@@ -20,6 +20,7 @@
  *   sfpe_roll_width           train/loader.py:31-57 (data_random_rotate's np.roll)
  *   sfpe_back_project         train/predict.py:230-293 (back_project_2D_2_3D)
  *   sfpe_find_bbox_3d         train/predict.py:94-199 (find_bbox_3d, is_far)
+ *   sfpe_find_obstacle        train/predict.py:33-81 (find_obstacle; scipy.ndimage.label)
  *   sfpe_params defaults      process/globals.py:3-13 (RES, VFOV, LIDAR_MIN_HEIGHT, ...)
  *
  * Conventions: every function returns 0 (SFPE_OK) or a negative sfpe_status; nothing throws
@@ -229,6 +230,17 @@ SFPE_API int sfpe_find_bbox_3d(sfpe_ctx* ctx, const void* d_distance, const void
                       const double* d_centroid3d, double x_min, double y_min, double res_rad_h,
                       double res_rad_v, double* d_boxes, int32_t* d_counts, int64_t cap,
                       double* d_out_pred, double* d_out_box, int32_t* d_n_boxes, void* stream);
+
+/* Heat map + clustering of the network's positive pixels (train/predict.py:33-81, find_obstacle).
+ * d_pred [n][height*width][n_channels] (`pred_dtype`), channel 1 = p(car).  Each pixel with p >= 0.5
+ * and row, column >= 2 adds 1 to heatmap[y-2:y+2, x-2:x+2]; cells with heat > 2 are clustered with
+ * 4-connectivity (scipy.ndimage.label's default); the cluster with the largest (max-min)*(max-min)
+ * box wins, the first in raster order on ties.  d_out [n][8] int32: found (0 = the reference's
+ * (None, None, None): area <= 100), centroid x, y, box left, top, right, bottom (shrunk by 2 as in
+ * :76), area.  d_scratch: [n][5][height*width] int32.  Integer work: exact. */
+SFPE_API int sfpe_find_obstacle(sfpe_ctx* ctx, const void* d_pred, int32_t pred_dtype, int32_t n_channels,
+                       int64_t n, int32_t height, int32_t width, int32_t* d_scratch, int32_t* d_out,
+                       void* stream);
 
 /* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
 SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);

@@ -351,3 +351,38 @@ def find_bbox_3d(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
         hs.append(abs(cand[i, 2] - cand[i + 1, 2]))
     pred[3], pred[4], pred[5], pred[6] = np.mean(yaws), np.mean(ls), np.mean(ws), np.mean(hs)   # :194-197
     return pred, cand
+
+
+MIN_HEAT = 2            # train/predict.py:30
+MIN_BBOX_AREA = 100     # train/predict.py:29
+
+
+def obstacle_heatmap(y_pred, input_shape):
+    """train/predict.py:34-52: 4x4 blocks of heat around positive pixels, thresholded.  heatmap[y-2:y+2, x-2:x+2]
+    with y < 2 or x < 2 is an EMPTY python slice (negative start), so those positives add nothing."""
+    h, w = input_shape[:2]
+    pred = np.reshape(y_pred[:, 1], (h, w))                                     # :34-35
+    heat = np.zeros((h, w))
+    for y, x in zip(*np.where(pred >= MIN_PROB)):                               # :36-48
+        if y >= 2 and x >= 2:
+            heat[y - 2:y + 2, x - 2:x + 2] += 1
+    heat[heat <= MIN_HEAT] = 0                                                  # :51
+    return heat
+
+
+def find_obstacle(y_pred, input_shape):
+    """train/predict.py:33-81.  Clusters are the 4-connected components of the thresholded heat map
+    (scipy.ndimage.label, default structure -- the reference's own dependency, :16,52), visited in label order."""
+    from scipy.ndimage import label
+    labels, n = label(obstacle_heatmap(y_pred, input_shape))                    # :52
+    best, max_area = None, 0
+    for k in range(1, n + 1):                                                   # :57-70
+        ys, xs = np.nonzero(labels == k)
+        area = int(xs.max() - xs.min()) * int(ys.max() - ys.min())
+        if area > max_area:
+            best, max_area = ((int(xs.min()), int(ys.min())), (int(xs.max()), int(ys.max()))), area
+    if max_area <= MIN_BBOX_AREA:                                               # :73-74
+        return None, None, None
+    box = ((best[0][0] + 2, best[0][1] + 2), (best[1][0] - 2, best[1][1] - 2))  # :76
+    centroid = (int((box[0][0] + box[1][0]) / 2.0), int((box[0][1] + box[1][1]) / 2.0))   # :77-78
+    return centroid, box, max_area

@@ -160,3 +160,30 @@ def find_bbox_3d_fn():
     if "fb" not in _cache:
         _cache["fb"] = _predict_functions(["is_far", "find_bbox_3d"])["find_bbox_3d"]
     return _cache["fb"]
+
+
+def find_obstacle_fn():
+    """The reference's find_obstacle (train/predict.py:33-81), unmodified, with scipy.ndimage.label as it imports it
+    (:16).  It spells the dtype `np.float`, an alias numpy 2 removed, so the name `np` it sees is numpy plus that one
+    alias (= the builtin float, which is what the alias was)."""
+    if "fo" in _cache:
+        return _cache["fo"]
+    import numpy as np
+    from scipy.ndimage import label
+
+    class _NumpyWithFloatAlias:
+        float = float
+
+        def __getattr__(self, name):
+            return getattr(np, name)
+
+    ns = _predict_functions([])
+    ns.update(np=_NumpyWithFloatAlias(), label=label)
+    path = os.path.join(_LIDAR, "train", "predict.py")
+    with open(path) as f:
+        lines = f.readlines()
+    start = next(i for i, ln in enumerate(lines) if ln.startswith("def find_obstacle("))
+    end = next(i for i in range(start + 1, len(lines)) if lines[i].startswith(("def ", "class ")))
+    exec(compile("\n" * start + "".join(lines[start:end]), path, "exec"), ns)
+    _cache["fo"] = ns["find_obstacle"]
+    return _cache["fo"]

@@ -511,3 +511,15 @@ extern "C" int sfpe_find_bbox_3d(sfpe_ctx* c, const void* d_distance, const void
                             d_out_box, d_n_boxes, (cudaStream_t)stream, &c->launches));
   return SFPE_OK;
 }
+
+extern "C" int sfpe_find_obstacle(sfpe_ctx* c, const void* d_pred, int32_t pred_dtype, int32_t n_channels, int64_t n,
+                                  int32_t height, int32_t width, int32_t* d_scratch, int32_t* d_out, void* stream) {
+  if (!c || n < 0 || height <= 0 || width <= 0 || n_channels < 2) return SFPE_ERR_INVALID_ARG;
+  if (pred_dtype != SFPE_F32 && pred_dtype != SFPE_F64) return SFPE_ERR_INVALID_ARG;
+  if (n > 0 && (!d_pred || !d_scratch || !d_out)) return SFPE_ERR_INVALID_ARG;
+  if (2ll * height * width > 220 * 1024 || n > 0x7fffffffll) return SFPE_ERR_UNSUPPORTED;   // flags live in shared memory
+  CK(c, cudaSetDevice(c->device));
+  CK(c, launch_find_obstacle(d_pred, pred_dtype, n_channels, n, height, width, d_scratch, d_out, (cudaStream_t)stream,
+                             &c->launches));
+  return SFPE_OK;
+}

@@ -72,6 +72,9 @@ cudaError_t launch_find_bbox_3d(const void* distance, const void* height, int dt
                                 double* boxes, int* counts, long long cap, double* out_pred, double* out_box, int* n_boxes,
                                 cudaStream_t st, long long* launches);
 
+cudaError_t launch_find_obstacle(const void* y_pred, int pred_dtype, int n_ch, long long n, int H, int W, int* scratch,
+                                 int* out, cudaStream_t st, long long* launches);
+
 // fused one-sweep-per-SM path -- sfpe_fused.cu
 struct FusedScratch {
   unsigned* entries;   // [grid][per_cta]

@@ -1,4 +1,5 @@
 // Consumers of the range scan that stay on the device:
+//   k_find_obstacle train/predict.py:33-81                heat map of positive pixels, 4-connected clusters, largest box
 //   k_find_bbox_3d  train/predict.py:94-199               per-pixel decode of the 3-D box corners + neighbour vote
 //   k_mask_update   create_lidar_invariant_mask.py:44-62  mask &= (reference == frame), every frame
 //   k_roll_width    train/loader.py:31-57                 np.roll(image, rotate_by, axis=1) per batch item
@@ -357,6 +358,94 @@ __global__ void __launch_bounds__(BOX_THREADS) k_find_bbox_3d(
   n_boxes[item] = K;
 }
 
+
+// ---- heat map + clustering (train/predict.py:33-81, find_obstacle) ------------------------------------------
+// One CTA per frame.  Positive pixels (p >= 0.5) each add 1 to the 4x4 block heatmap[y-2:y+2, x-2:x+2]; a python
+// slice that starts below 0 is empty, so positives with y < 2 or x < 2 add nothing.  Cells with heat > 2 are
+// clustered with 4-connectivity (scipy.ndimage.label's default): union-find over `labels` in global scratch, root =
+// smallest pixel index = first pixel in raster order, which is also scipy's label order.  The cluster with the
+// largest (max-min) x (max-min) box wins, the earliest label on ties (`area > max_area`).
+constexpr int OBS_THREADS = 1024;
+
+__device__ __forceinline__ int uf_find(const int* lab, int p) {
+  int q = ((volatile const int*)lab)[p];
+  while (q != p) { p = q; q = ((volatile const int*)lab)[p]; }
+  return p;
+}
+__device__ __forceinline__ void uf_union(int* lab, int a, int b) {
+  for (;;) {
+    a = uf_find(lab, a);
+    b = uf_find(lab, b);
+    if (a == b) return;
+    if (a < b) { const int t = a; a = b; b = t; }     // a > b: hang a under b
+    const int old = atomicMin(lab + a, b);
+    if (old == a) return;
+    a = old;                                            // somebody else re-rooted a meanwhile: merge that root too
+  }
+}
+
+template <typename TP>
+__global__ void __launch_bounds__(OBS_THREADS) k_find_obstacle(const TP* __restrict__ y_pred, int n_ch, int H, int W,
+                                                               int* __restrict__ scratch_all, int* __restrict__ out) {
+  extern __shared__ unsigned char sm[];   // [H*W] positive flags, then [H*W] foreground flags
+  __shared__ unsigned long long s_best;
+  const long long item = blockIdx.x;
+  const int tid = threadIdx.x, N = H * W;
+  const TP* yp = y_pred + item * (long long)N * n_ch;
+  unsigned char* posf = sm;
+  unsigned char* fg = sm + N;
+  int* lab = scratch_all + item * 5ll * N;
+  int* minx = lab + N; int* maxx = minx + N; int* miny = maxx + N; int* maxy = miny + N;
+  if (tid == 0) s_best = 0ull;
+  for (int p = tid; p < N; p += OBS_THREADS) posf[p] = (double)yp[(long long)p * n_ch + 1] >= 0.5;
+  __syncthreads();
+  for (int p = tid; p < N; p += OBS_THREADS) {
+    const int r = p / W, c = p - r * W;
+    int heat = 0;
+    for (int y = max(r - 1, 2); y <= min(r + 2, H - 1); ++y)
+      for (int x = max(c - 1, 2); x <= min(c + 2, W - 1); ++x) heat += posf[y * W + x];
+    const bool f = heat > 2;                            // MIN_HEAT, predict.py:30,52
+    fg[p] = f;
+    lab[p] = f ? p : -1;
+    minx[p] = W; maxx[p] = -1; miny[p] = H; maxy[p] = -1;
+  }
+  __syncthreads();
+  for (int p = tid; p < N; p += OBS_THREADS)
+    if (fg[p]) {
+      const int r = p / W, c = p - r * W;
+      if (c > 0 && fg[p - 1]) uf_union(lab, p, p - 1);
+      if (r > 0 && fg[p - W]) uf_union(lab, p, p - W);
+    }
+  __syncthreads();
+  for (int p = tid; p < N; p += OBS_THREADS)
+    if (fg[p]) {
+      const int root = uf_find(lab, p), r = p / W, c = p - r * W;
+      atomicMin(minx + root, c); atomicMax(maxx + root, c);
+      atomicMin(miny + root, r); atomicMax(maxy + root, r);
+    }
+  __syncthreads();
+  for (int p = tid; p < N; p += OBS_THREADS)
+    if (fg[p] && ((volatile int*)lab)[p] == p) {
+      const unsigned long long area = (unsigned long long)(maxx[p] - minx[p]) * (unsigned long long)(maxy[p] - miny[p]);
+      if (area > 0) atomicMax(&s_best, (area << 32) | (unsigned)(0x7fffffff - p));
+    }
+  __syncthreads();
+  if (tid != 0) return;
+  int* o = out + 8 * item;   // found, centroid x, y, left, top, right, bottom, area
+  const long long area = (long long)(s_best >> 32);
+  if (area <= 100) {         // MIN_BBOX_AREA, predict.py:29,73
+    for (int k = 0; k < 8; ++k) o[k] = 0;
+    return;
+  }
+  const int root = 0x7fffffff - (int)(unsigned)(s_best & 0xffffffffu);
+  const int l = minx[root] + 2, t = miny[root] + 2, r = maxx[root] - 2, b = maxy[root] - 2;   // predict.py:76
+  o[0] = 1;
+  o[1] = (int)((l + r) / 2.0);
+  o[2] = (int)((t + b) / 2.0);
+  o[3] = l; o[4] = t; o[5] = r; o[6] = b;
+  o[7] = (int)area;
+}
+
 }  // namespace
 
 cudaError_t launch_mask_update(const void* ref, const void* frames, int dtype, long long n_frames, long long frame_stride,
@@ -424,6 +513,24 @@ cudaError_t launch_find_bbox_3d(const void* distance, const void* height, int dt
   else if (pred_dtype == SFPE_F32) SFPE_BOX_LAUNCH(double, float);
   else SFPE_BOX_LAUNCH(double, double);
 #undef SFPE_BOX_LAUNCH
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_find_obstacle(const void* y_pred, int pred_dtype, int n_ch, long long n, int H, int W, int* scratch,
+                                 int* out, cudaStream_t st, long long* launches) {
+  if (n <= 0) return cudaSuccess;
+  const size_t smem = 2 * (size_t)H * W;
+  cudaError_t e;
+  if (pred_dtype == SFPE_F32) {
+    e = cudaFuncSetAttribute(k_find_obstacle<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_find_obstacle<float><<<(unsigned)n, OBS_THREADS, smem, st>>>((const float*)y_pred, n_ch, H, W, scratch, out);
+  } else {
+    e = cudaFuncSetAttribute(k_find_obstacle<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_find_obstacle<double><<<(unsigned)n, OBS_THREADS, smem, st>>>((const double*)y_pred, n_ch, H, W, scratch, out);
+  }
   ++*launches;
   return cudaGetLastError();
 }

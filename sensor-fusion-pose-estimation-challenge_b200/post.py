@@ -2,6 +2,7 @@
 
     back_project_2D_2_3D      train/predict.py:230-293      -> sfpe_back_project
     InvariantMask.update      process/create_lidar_invariant_mask.py:44-62 -> sfpe_invariant_mask_update
+    find_obstacle             train/predict.py:33-81 -> sfpe_find_obstacle
     find_bbox_3d              train/predict.py:94-199 (+ is_far :83-92) -> sfpe_find_bbox_3d
     roll_width                train/loader.py:47-50 (np.roll(image, rotate_by, axis=1)) -> sfpe_roll_width
 
@@ -227,3 +228,36 @@ def find_bbox_3d(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
     if int(n[0]) == 0:
         return np.zeros(7), None
     return pred[0].cpu().numpy(), box[0].cpu().numpy()
+
+
+def find_obstacle_device(y_pred, height, width, stream=None):
+    """Device form of find_obstacle for a batch: y_pred (B, height*width, n_channels) float32/float64 CUDA tensor.
+    Returns an int32 device tensor (B, 8): found, centroid x, y, box left, top, right, bottom, area."""
+    torch = _torch()
+    y_pred = y_pred.contiguous()
+    if y_pred.dim() != 3 or y_pred.shape[1] != height * width or y_pred.shape[2] < 2 or not y_pred.is_cuda:
+        raise ValueError("y_pred must be a CUDA tensor (B, height*width, n_channels >= 2)")
+    B = y_pred.shape[0]
+    scratch = torch.empty((B, 5, height * width), dtype=torch.int32, device=y_pred.device)
+    out = torch.empty((B, 8), dtype=torch.int32, device=y_pred.device)
+    pr = _projector(y_pred.device)
+    rc = pr.lib.sfpe_find_obstacle(pr._ctx, C.c_void_p(y_pred.data_ptr()), _dtype_code(y_pred), y_pred.shape[2], B, height,
+                                   width, C.c_void_p(scratch.data_ptr()), C.c_void_p(out.data_ptr()), _stream_ptr(stream))
+    _lib.check(rc, pr._ctx)
+    torch.cuda.current_stream().synchronize() if stream is None else stream.synchronize()   # scratch is freed on return
+    return out
+
+
+def find_obstacle(y_pred, input_shape):
+    """Reference signature (train/predict.py:33): y_pred (height*width, n_classes) numpy, input_shape = (height,
+    width, ...).  Returns ((centroid_x, centroid_y), ((left, top), (right, bottom)), area) or (None, None, None)."""
+    torch = _torch()
+    pr = _projector(None)
+    y = np.ascontiguousarray(y_pred)
+    if y.dtype not in (np.float32, np.float64):
+        y = y.astype(np.float64)
+    H, W = int(input_shape[0]), int(input_shape[1])
+    o = find_obstacle_device(torch.as_tensor(y.reshape(1, H * W, -1)).to(torch.device("cuda", pr.device)), H, W)[0].cpu().numpy()
+    if not o[0]:
+        return None, None, None
+    return (int(o[1]), int(o[2])), ((int(o[3]), int(o[4])), (int(o[5]), int(o[6]))), int(o[7])

@@ -182,3 +182,28 @@ def make_bbox_decode_case(seed=0, height=32, width=1801, noise=0.35, strays=6):
     bbox_2d = ((cx0 - half_w, cy0 - half_h), (cx0 + half_w, cy0 + half_h))
     centroid_3d = centre + rng.normal(0, 0.3, 3)
     return dist, hgt, y.reshape(height * width, 26), bbox_2d, centroid_3d
+
+
+def make_obstacle_case(seed=0, height=32, width=1801, blobs=4, speckle=0.002):
+    """Synthetic 2-class FCN output (height*width, 2) float32 for find_obstacle (train/predict.py:33-81): a few
+    ragged blobs of positive pixels (some touching the image border, some joined by thin bridges, some of equal
+    size), plus isolated speckle that stays under the heat threshold.  seed % 4 == 3 gives a frame whose largest
+    cluster is too small (the reference returns (None, None, None))."""
+    rng = np.random.default_rng(3000 + seed)
+    p = rng.uniform(0.0, 0.49, (height, width)).astype(np.float32)
+    small = seed % 4 == 3
+    for b in range(blobs):
+        bw, bh = (int(rng.integers(3, 8)), int(rng.integers(2, 5))) if small else (int(rng.integers(8, 40)), int(rng.integers(4, 14)))
+        x0 = int(rng.integers(0, width - bw)) if b else 0                      # the first blob touches the left border
+        y0 = int(rng.integers(0, height - bh)) if b != 1 else height - bh      # the second the bottom border
+        keep = rng.random((bh, bw)) < 0.8
+        p[y0:y0 + bh, x0:x0 + bw][keep] = rng.uniform(0.5, 1.0, keep.sum())
+        if b == 2 and not small:                                               # a copy of equal size further right: tie on area
+            x1 = min(x0 + bw + 60, width - bw)
+            p[y0:y0 + bh, x1:x1 + bw] = p[y0:y0 + bh, x0:x0 + bw]
+    spk = rng.random((height, width)) < speckle
+    p[spk] = 0.9
+    y = np.zeros((height * width, 2), np.float32)
+    y[:, 1] = p.ravel()
+    y[:, 0] = 1 - y[:, 1]
+    return y

@@ -117,8 +117,20 @@ def bbox_decode_case(name, seeds):
     print(name, len(seeds), "cases ->", os.path.getsize(path) // 1024, "KiB")
 
 
+def obstacle_case(name, seeds):
+    """Reference find_obstacle (train/predict.py:33-81) on synthetic 2-class outputs: found, centroid, box, area."""
+    rows = []
+    for seed in seeds:
+        c, b, a = rl.find_obstacle_fn()(synth.make_obstacle_case(seed=seed), (32, 1801, 3))
+        rows.append([seed, 0, 0, 0, 0, 0, 0, 0, 0] if c is None else
+                    [seed, 1, c[0], c[1], b[0][0], b[0][1], b[1][0], b[1][1], a])
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), rows=np.array(rows, dtype=np.int64))
+    print(name, len(seeds), "cases")
+
+
 def main():
     back_project_case("back_project_seed0", 0)
+    obstacle_case("find_obstacle", list(range(12)))
     bbox_decode_case("bbox_decode", [0, 1, 2, 3])
     run_case("hdl32_seed0", synth.make_sweep("hdl32", seed=0))
     run_case("hdl32_seed1_shuffled_dropout", synth.make_sweep("hdl32", seed=1, shuffle=True, dropout=0.05))

@@ -159,3 +159,47 @@ def test_find_bbox_3d_device_batch_and_overflow(post, torch):
         np.testing.assert_allclose(pred[i].cpu().numpy(), want_pred, rtol=0, atol=1e-9)
     _, _, n_small = post.find_bbox_3d_device(y, bb, c3, range_scan=torch.as_tensor(scan).cuda(), cap=8)
     assert (n_small.cpu().numpy() == -1).all()                                          # scratch too small: flagged
+
+
+def _obstacle_tuple(res):
+    c, b, a = res
+    return [0] * 8 if c is None else [int(v) for v in (1, c[0], c[1], b[0][0], b[0][1], b[1][0], b[1][1], a)]
+
+
+def test_find_obstacle_vs_reference_golden(post):
+    synth = load_sub("synth")
+    for row in golden("find_obstacle")["rows"]:
+        y = synth.make_obstacle_case(seed=int(row[0]))
+        assert _obstacle_tuple(post.find_obstacle(y, (32, 1801, 3))) == [int(v) for v in row[1:]]
+        assert _obstacle_tuple(post.find_obstacle(y.astype(np.float64), (32, 1801, 3))) == [int(v) for v in row[1:]]
+
+
+def test_find_obstacle_batch_shapes_ties_and_snakes(post, torch):
+    """Equal-area clusters (first in raster order wins), a one-pixel-wide spiral (worst case for label
+    propagation), U shapes that merge late, 3-channel output, everything positive, nothing positive."""
+    H, W = 32, 1801
+    frames = []
+    p = np.zeros((H, W), np.float32)
+    p[10:20, 1000:1030] = 1; p[4:14, 200:230] = 1; p[4:14, 600:630] = 1          # three equal boxes: the one at row 4, col 200
+    frames.append(p)
+    p = np.zeros((H, W), np.float32)
+    for r in range(2, 30, 6):                                                     # a snake: long rows joined at alternating ends
+        p[r:r + 2, 2:1790] = 1
+        col = 1786 if (r // 6) % 2 == 0 else 2
+        p[r:r + 8, col:col + 3] = 1
+    frames.append(p)
+    p = np.zeros((H, W), np.float32)
+    p[3:25, 50:54] = 1; p[3:25, 90:94] = 1; p[22:25, 50:94] = 1                    # a U: two arms that meet at the bottom
+    p[5:9, 1500:1530] = 1
+    frames.append(p)
+    frames.append(np.ones((H, W), np.float32))
+    frames.append(np.zeros((H, W), np.float32))
+    rng = np.random.default_rng(3)
+    frames.append((rng.random((H, W)) < 0.25).astype(np.float32))                  # dense noise: many ragged clusters
+    y = np.zeros((len(frames), H * W, 3), np.float32)
+    for i, f in enumerate(frames):
+        y[i, :, 1] = f.ravel()
+    out = post.find_obstacle_device(torch.as_tensor(y).cuda(), H, W).cpu().numpy()
+    for i in range(len(frames)):
+        assert out[i].tolist() == _obstacle_tuple(lo.find_obstacle(y[i], (H, W, 3))), i
+    assert out[0, 0] == 1 and out[4, 0] == 0

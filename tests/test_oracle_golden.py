@@ -163,3 +163,24 @@ def test_find_bbox_3d_equals_live_reference(synth):
     far = rl.find_bbox_3d_fn()(d64, h64, y, bb, c3 + 100.0)          # every set is far: zeros(7), None
     assert far[1] is None and not far[0].any()
     assert lo.find_bbox_3d(d64, h64, y, bb, c3 + 100.0)[1] is None
+
+
+def _obstacle_tuple(res):
+    c, b, a = res
+    return [0] * 8 if c is None else [1, c[0], c[1], b[0][0], b[0][1], b[1][0], b[1][1], a]
+
+
+def test_find_obstacle_matches_reference_golden(synth):
+    """oracle.find_obstacle vs outputs of the reference's own find_obstacle (train/predict.py:33-81)."""
+    rows = golden("find_obstacle")["rows"]
+    assert (rows[:, 1] == 0).sum() >= 2 and (rows[:, 1] == 1).sum() >= 6
+    for row in rows:
+        got = _obstacle_tuple(lo.find_obstacle(synth.make_obstacle_case(seed=int(row[0])), (32, 1801, 3)))
+        assert [int(v) for v in got] == [int(v) for v in row[1:]]
+
+
+@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+def test_find_obstacle_equals_live_reference(synth):
+    for seed in (40, 41, 42):
+        y = synth.make_obstacle_case(seed=seed, blobs=7, speckle=0.01)
+        assert _obstacle_tuple(rl.find_obstacle_fn()(y, (32, 1801, 3))) == _obstacle_tuple(lo.find_obstacle(y, (32, 1801, 3)))
