@@ -308,7 +308,7 @@ def decode_boxes(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
     row_has[pos_rows] = True
     col_has[pos_cols] = True
     (ulx, uly), (lrx, lry) = bbox_2d                                            # :99
-    c3 = np.asarray(centroid_3d, dtype=np.float64)
+    c3 = np.asarray(centroid_3d, dtype=np.float64)[:3]                          # is_far reads [0], [1], [2] (:87-89)
     boxes = []
     for x in range(max(ulx - 100, 0), min(lrx + 100, w)):                       # :103 (outside the image nothing matches)
         if not col_has[x]:
@@ -386,3 +386,18 @@ def find_obstacle(y_pred, input_shape):
     box = ((best[0][0] + 2, best[0][1] + 2), (best[1][0] - 2, best[1][1] - 2))  # :76
     centroid = (int((box[0][0] + box[1][0]) / 2.0), int((box[0][1] + box[1][1]) / 2.0))   # :77-78
     return centroid, box, max_area
+
+
+def predict_tail(prediction, distance, height, fns=None):
+    """What predict_point_cloud does after model.predict (train/predict.py:347-362, use_regression=True), composed
+    from the three restatements above (or, for pinning, from the reference's own three functions in `fns`)."""
+    f_obstacle, f_back, f_bbox = fns or (find_obstacle, back_project, find_bbox_3d)
+    centroid_2d, bbox_2d, _ = f_obstacle(prediction, distance.shape + (3,))     # :347
+    pred = np.array([0, 0, 0, 0])                                               # :348
+    if centroid_2d is not None:
+        centroids = np.array(centroid_2d).reshape(1, 2)                         # :351 (integer arrays, as there)
+        bboxes = np.array(bbox_2d).reshape(1, 4)
+        centroid_3d = f_back(centroids, bboxes, distance[None], height[None])[0]   # :355
+        if not (centroid_3d[0] == 0. and centroid_3d[1] == 0.):                 # :358
+            pred, _ = f_bbox(distance, height, prediction, bbox_2d, centroid_3d)   # :359
+    return pred

@@ -2,6 +2,7 @@
 
     back_project_2D_2_3D      train/predict.py:230-293      -> sfpe_back_project
     InvariantMask.update      process/create_lidar_invariant_mask.py:44-62 -> sfpe_invariant_mask_update
+    locate_obstacles          train/predict.py:347-362 (the part of predict_point_cloud after model.predict)
     find_obstacle             train/predict.py:33-81 -> sfpe_find_obstacle
     find_bbox_3d              train/predict.py:94-199 (+ is_far :83-92) -> sfpe_find_bbox_3d
     roll_width                train/loader.py:47-50 (np.roll(image, rotate_by, axis=1)) -> sfpe_roll_width
@@ -37,6 +38,15 @@ def _stream_ptr(stream):
     torch = _torch()
     s = stream if stream is not None else torch.cuda.current_stream()
     return C.c_void_p(s.cuda_stream)
+
+
+def _release_on(stream, *tensors):
+    """Scratch tensors die when the caller returns.  torch's caching allocator hands a block back only to work queued
+    later on the stream it was allocated on, so nothing is needed for the current stream; a kernel launched on
+    another stream has to be recorded on the block."""
+    if stream is not None:
+        for t in tensors:
+            t.record_stream(stream)
 
 
 def _projector(device):
@@ -202,7 +212,7 @@ def find_bbox_3d_device(y_pred, bbox_2d, centroid_3d, range_scan=None, distance=
         C.c_void_p(counts.data_ptr()), cap, C.c_void_p(pred.data_ptr()), C.c_void_p(box.data_ptr()),
         C.c_void_p(n_boxes.data_ptr()), _stream_ptr(stream))
     _lib.check(rc, pr._ctx)
-    torch.cuda.current_stream().synchronize() if stream is None else stream.synchronize()   # scratch is freed on return
+    _release_on(stream, boxes, counts)
     return pred, box, n_boxes
 
 
@@ -244,7 +254,7 @@ def find_obstacle_device(y_pred, height, width, stream=None):
     rc = pr.lib.sfpe_find_obstacle(pr._ctx, C.c_void_p(y_pred.data_ptr()), _dtype_code(y_pred), y_pred.shape[2], B, height,
                                    width, C.c_void_p(scratch.data_ptr()), C.c_void_p(out.data_ptr()), _stream_ptr(stream))
     _lib.check(rc, pr._ctx)
-    torch.cuda.current_stream().synchronize() if stream is None else stream.synchronize()   # scratch is freed on return
+    _release_on(stream, scratch)
     return out
 
 
@@ -261,3 +271,41 @@ def find_obstacle(y_pred, input_shape):
     if not o[0]:
         return None, None, None
     return (int(o[1]), int(o[2])), ((int(o[3]), int(o[4])), (int(o[5]), int(o[6]))), int(o[7])
+
+
+def locate_obstacles(prediction, range_scan, stream=None):
+    """Everything predict_point_cloud does after `model.predict` (train/predict.py:347-362, use_regression=True),
+    for a device-resident batch and without leaving the device: prediction (B, H*W, 26) as the FCN returns it,
+    range_scan (B, H, W, 3) as the projector wrote it.  find_obstacle -> back_project_2D_2_3D -> find_bbox_3d.
+    Returns (pred (B,7) float64: x, y, z, yaw, length, width, height; found (B,) bool).  Frames without a cluster,
+    without a valid pixel in the cluster's box, or without a corner set near the centroid give zeros / False
+    (the reference returns [0,0,0,0] or zeros(7) there)."""
+    torch = _torch()
+    B, H, W, _ = range_scan.shape
+    obs = find_obstacle_device(prediction, H, W, stream=stream)
+    centroids = obs[:, 1:3].to(torch.float64).contiguous()
+    bboxes = obs[:, 3:7].to(torch.float64).contiguous()
+    xyz, _ = back_project_device(centroids, bboxes, range_scan=range_scan, stream=stream)
+    pred, _, n_boxes = find_bbox_3d_device(prediction, obs[:, 3:7].contiguous(), xyz[:, :3].contiguous(),
+                                           range_scan=range_scan, stream=stream)
+    found = (obs[:, 0] != 0) & ~((xyz[:, 0] == 0) & (xyz[:, 1] == 0)) & (n_boxes > 0)      # :349, :358, :137
+    return torch.where(found[:, None], pred, torch.zeros_like(pred)), found
+
+
+def predict_point_cloud_tail(prediction, points_2d, use_regression=True):
+    """One frame, reference types: `prediction` = model.predict(...)[0] (H*W, 26), `points_2d` = the dict returned by
+    generate_lidar_2d_front_view.  Returns what predict_point_cloud returns (train/predict.py:347-362)."""
+    d = np.asarray(points_2d["distance_float"])
+    h = np.asarray(points_2d["height_float"])
+    centroid_2d, bbox_2d, _ = find_obstacle(prediction, d.shape)
+    pred = np.array([0, 0, 0, 0])
+    if centroid_2d is not None:
+        centroids = np.array(centroid_2d).reshape(1, 2)
+        bboxes = np.array(bbox_2d).reshape(1, 4)
+        centroid_3d = back_project_2D_2_3D(centroids, bboxes, d[None], h[None])[0]
+        if use_regression:
+            if not (centroid_3d[0] == 0. and centroid_3d[1] == 0.):
+                pred, _ = find_bbox_3d(d, h, prediction, bbox_2d, centroid_3d)
+        else:
+            pred = centroid_3d[0]
+    return pred

@@ -207,3 +207,21 @@ def make_obstacle_case(seed=0, height=32, width=1801, blobs=4, speckle=0.002):
     y[:, 1] = p.ravel()
     y[:, 0] = 1 - y[:, 1]
     return y
+
+
+def make_detection_case(seed=0):
+    """A frame for the whole post-network chain (find_obstacle -> back_project_2D_2_3D -> find_bbox_3d): the box-decode
+    case with its blob filled densely enough to form one cluster above the area threshold, and the range scan
+    hollowed out under the cluster's centre so that the back-projection has to search its box."""
+    dist, hgt, y, bb, _ = make_bbox_decode_case(seed=seed, strays=0)
+    rng = np.random.default_rng(4000 + seed)
+    H, W = dist.shape
+    (l, t), (r, b) = bb
+    l, r, t, b = l - 6, r + 6, max(t - 2, 2), min(b + 2, H - 1)
+    y3 = y.reshape(H, W, 26)
+    y3[t:b + 1, l:r + 1, 1] = rng.uniform(0.55, 1.0, (b - t + 1, r - l + 1))
+    cy, cx = (t + b) // 2, (l + r) // 2
+    dist[cy - 1:cy + 2, cx - 2:cx + 3] = 0       # no return under the centroid (seed % 3 == 2: nowhere in the box)
+    if seed % 3 == 2:
+        dist[max(t - 3, 0):b + 4, l - 3:r + 4] = 0
+    return dist, hgt, y3.reshape(H * W, 26)

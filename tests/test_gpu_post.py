@@ -203,3 +203,25 @@ def test_find_obstacle_batch_shapes_ties_and_snakes(post, torch):
     for i in range(len(frames)):
         assert out[i].tolist() == _obstacle_tuple(lo.find_obstacle(y[i], (H, W, 3))), i
     assert out[0, 0] == 1 and out[4, 0] == 0
+
+
+def test_post_network_chain_on_device(post, torch):
+    """locate_obstacles (batch, nothing leaves the device) and predict_point_cloud_tail (one frame, reference types)
+    against the oracle's composition of the three restatements."""
+    synth = load_sub("synth")
+    cases = [synth.make_detection_case(seed) for seed in range(6)]
+    want = [lo.predict_tail(y, d.astype(np.float64), h.astype(np.float64)) for d, h, y in cases]
+    assert {len(w) for w in want} == {4, 7}
+    scan = np.zeros((len(cases), 32, 1801, 3), np.float32)
+    for i, (d, h, _) in enumerate(cases):
+        scan[i, ..., 0], scan[i, ..., 1] = d, h
+    pred, found = post.locate_obstacles(torch.as_tensor(np.stack([c[2] for c in cases])).cuda(), torch.as_tensor(scan).cuda())
+    pred, found = pred.cpu().numpy(), found.cpu().numpy()
+    for i, w in enumerate(want):
+        assert bool(found[i]) == (len(w) == 7)
+        np.testing.assert_allclose(pred[i], w if len(w) == 7 else np.zeros(7), rtol=0, atol=1e-9)
+    for i in (0, 2):
+        d, h, y = cases[i]
+        got = post.predict_point_cloud_tail(y, {"distance_float": d.astype(np.float64), "height_float": h.astype(np.float64)})
+        assert got.shape == want[i].shape
+        np.testing.assert_allclose(got, want[i], rtol=0, atol=1e-9)

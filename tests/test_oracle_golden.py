@@ -184,3 +184,17 @@ def test_find_obstacle_equals_live_reference(synth):
     for seed in (40, 41, 42):
         y = synth.make_obstacle_case(seed=seed, blobs=7, speckle=0.01)
         assert _obstacle_tuple(rl.find_obstacle_fn()(y, (32, 1801, 3))) == _obstacle_tuple(lo.find_obstacle(y, (32, 1801, 3)))
+
+
+@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+def test_post_network_chain_equals_live_reference(synth):
+    """find_obstacle -> back_project_2D_2_3D -> find_bbox_3d as predict_point_cloud chains them (:347-362)."""
+    fns = (rl.find_obstacle_fn(), rl.back_project_fn(), rl.find_bbox_3d_fn())
+    kinds = set()
+    for seed in range(4):
+        dist, hgt, y = synth.make_detection_case(seed)
+        d, h = dist.astype(np.float64), hgt.astype(np.float64)
+        want, got = lo.predict_tail(y, d, h, fns), lo.predict_tail(y, d, h)
+        assert want.shape == got.shape and np.array_equal(want, got)
+        kinds.add(len(got))
+    assert kinds == {4, 7}
