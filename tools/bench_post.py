@@ -82,6 +82,34 @@ def main():
     ms = timed(torch, bp, a.reps)
     line("k_back_project<float> (+2 small copies, 2 allocations)", ms, 0, {"items/s": round(B / ms * 1e3)})
 
+    # the post-network chain on a batch of FCN outputs (B, H*W, 26) float32: 6 MB per frame
+    del rs, out, d_scan
+    torch.cuda.empty_cache()
+    Bn = min(B, 296)
+    cases = [synth.make_detection_case(s) for s in range(8)]
+    y = torch.as_tensor(np.stack([c[2] for c in cases])).cuda().repeat((Bn + 7) // 8, 1, 1)[:Bn].contiguous()
+    sc = np.zeros((8, H, W, 3), np.float32)
+    for i, c in enumerate(cases):
+        sc[i, ..., 0], sc[i, ..., 1] = c[0], c[1]
+    scan2 = torch.as_tensor(sc).cuda().repeat((Bn + 7) // 8, 1, 1, 1)[:Bn].contiguous()
+    pred_bytes = Bn * H * W * 26 * 4
+
+    def as_frames(name, ms, nbytes):
+        gb = nbytes / ms / 1e6
+        print(json.dumps({"kernel": name, "frames": Bn, "ms": round(ms, 4), "frames/s": round(Bn / ms * 1e3),
+                          "network_output_GB/s": round(gb, 1), "frac_of_hbm_peak": round(gb / peak, 3) if peak else None}))
+    ms = timed(torch, lambda: post.find_obstacle_device(y, H, W), a.reps)
+    as_frames("k_find_obstacle<float> (+ scratch allocation)", ms, pred_bytes)
+    obs = post.find_obstacle_device(y, H, W)
+    cen = obs[:, 1:3].double().contiguous()
+    box = obs[:, 3:7].double().contiguous()
+    xyz, _ = post.back_project_device(cen.clone(), box.clone(), range_scan=scan2)
+    bb2, c3 = obs[:, 3:7].contiguous(), xyz[:, :3].contiguous()
+    ms = timed(torch, lambda: post.find_bbox_3d_device(y, bb2, c3, range_scan=scan2, cap=4096), a.reps)
+    as_frames("k_find_bbox_3d<float,float> (+ scratch allocation)", ms, pred_bytes)
+    ms = timed(torch, lambda: post.locate_obstacles(y, scan2), a.reps)
+    as_frames("locate_obstacles: find_obstacle -> back_project -> find_bbox_3d (+ torch glue)", ms, 2 * pred_bytes)
+
 
 if __name__ == "__main__":
     main()
