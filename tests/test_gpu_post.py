@@ -225,3 +225,30 @@ def test_post_network_chain_on_device(post, torch):
         got = post.predict_point_cloud_tail(y, {"distance_float": d.astype(np.float64), "height_float": h.astype(np.float64)})
         assert got.shape == want[i].shape
         np.testing.assert_allclose(got, want[i], rtol=0, atol=1e-9)
+
+
+@pytest.mark.parametrize("cmap,pickle", [("jet", True), ("gray", False), (None, True)])
+def test_velodyne_message_renderer_equals_the_drop_ins(cmap, pickle):
+    """handle_msg's PointCloud2 branch (extract_rosbag.py:162-187) in one device pass == the two drop-in calls the
+    reference makes there, on the points its per-point decode would produce."""
+    pkg = load_pkg()
+    synth = load_sub("synth")
+    er = load_sub("process.extract_rosbag")
+    pts = synth.make_sweep("hdl32", seed=12, n_az=600)
+    P = synth.as_reference_array(pts)
+    r = er.VelodyneMessageRenderer(topdown_res=2, topdown_max_range=120, cmap=cmap, pickle=pickle)
+    density, images = r(synth.make_pointcloud2_blob(pts))
+    want_density = pkg.generate_birds_eye_view(P, 0, res=(2, 2), max_range=120, cmap=cmap or "gray").astype(np.uint8)
+    want = pkg.generate_lidar_2d_front_view(P, cmap=cmap)
+    assert density.dtype == np.uint8 and np.array_equal(density, want_density)
+    kinds = ["intensity", "distance", "height"]
+    assert sorted(images) == sorted(kinds + ([k + "_float" for k in kinds] if pickle else []))
+    for k in images:
+        assert images[k].dtype == want[k].dtype and np.array_equal(images[k], want[k]), k
+    if pickle:
+        ref = lo.front_view(P)
+        for k in kinds:
+            assert np.array_equal(images[k + "_float"], ref[k])
+    bad = np.vstack([pts, np.zeros((1, 4), np.float32)])                       # a point at the origin
+    with pytest.raises(IndexError):
+        r(synth.make_pointcloud2_blob(bad))
