@@ -171,7 +171,7 @@ def run_reference(a):
                                    % (per_step, len(times), cores)},
         "e2e": {"value": val, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(a):
@@ -293,7 +293,7 @@ def run_ours(a):
             line["cpu_baseline"] = {"value": n / dt, "unit": "sweeps/s", "cores": ref.cores, "kind": "port",
                                     "sample": "%d sweeps of the same workload, numpy port of the reference in %d "
                                               "processes (%.1f s)" % (n, ref.cores, dt)}
-        print(json.dumps(line))
+        emit(line)
     pr.close()
     if world > 1:
         dist.destroy_process_group()
@@ -323,7 +323,30 @@ def run_e2e(a, pkg, pr, pin_in, dev, world):
             "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; PCIe bound" % hb.chunk}
 
 
+_JSON_FD = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout.  Native libraries print there too (NCCL's version banner under
+    torchrun, for one), so file descriptor 1 is pointed at stderr for the whole run and the JSON line goes to a
+    private duplicate of the original stdout."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
