@@ -222,14 +222,16 @@ SFPE_API int sfpe_back_project(sfpe_ctx* ctx, double* d_centroids, double* d_bbo
  * d_out_pred[i] = x, y, z (mean corner), yaw, length, width, height.  d_n_boxes[i] = sets kept
  * (0: d_out_pred = 0 and no box, the reference's `None`; -1: more than `cap` sets, nothing written).
  * Scratch: d_boxes [n][cap][24] float64, d_counts [n][cap] int32.  Images addressed like
- * sfpe_back_project.  Decisions and sums follow the reference's order; the trigonometry and the
+ * sfpe_back_project.  d_posbits: NULL, or the positive-pixel bits sfpe_find_obstacle wrote for the
+ * same d_pred (saves the second pass over the tensor).  Decisions and sums follow the reference's order; the trigonometry and the
  * 3x3 products are the device's fp64 (test tolerance 1e-9 absolute on metres / radians). */
 SFPE_API int sfpe_find_bbox_3d(sfpe_ctx* ctx, const void* d_distance, const void* d_height, int32_t dtype,
                       int64_t frame_stride, int32_t pix_stride, const void* d_pred, int32_t pred_dtype,
                       int64_t n, int32_t height, int32_t width, const int32_t* d_bbox2d,
                       const double* d_centroid3d, double x_min, double y_min, double res_rad_h,
                       double res_rad_v, double* d_boxes, int32_t* d_counts, int64_t cap,
-                      double* d_out_pred, double* d_out_box, int32_t* d_n_boxes, void* stream);
+                      double* d_out_pred, double* d_out_box, int32_t* d_n_boxes,
+                      const uint32_t* d_posbits, void* stream);
 
 /* Heat map + clustering of the network's positive pixels (train/predict.py:33-81, find_obstacle).
  * d_pred [n][height*width][n_channels] (`pred_dtype`), channel 1 = p(car).  Each pixel with p >= 0.5
@@ -237,10 +239,11 @@ SFPE_API int sfpe_find_bbox_3d(sfpe_ctx* ctx, const void* d_distance, const void
  * 4-connectivity (scipy.ndimage.label's default); the cluster with the largest (max-min)*(max-min)
  * box wins, the first in raster order on ties.  d_out [n][8] int32: found (0 = the reference's
  * (None, None, None): area <= 100), centroid x, y, box left, top, right, bottom (shrunk by 2 as in
- * :76), area.  d_scratch: [n][5][height*width] int32.  Integer work: exact. */
+ * :76), area.  d_scratch: [n][5][height*width] int32.  d_posbits: NULL, or [n][ceil(height*width/32)]
+ * words that receive one bit per pixel (p >= 0.5), for sfpe_find_bbox_3d.  Integer work: exact. */
 SFPE_API int sfpe_find_obstacle(sfpe_ctx* ctx, const void* d_pred, int32_t pred_dtype, int32_t n_channels,
                        int64_t n, int32_t height, int32_t width, int32_t* d_scratch, int32_t* d_out,
-                       void* stream);
+                       uint32_t* d_posbits, void* stream);
 
 /* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
 SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);

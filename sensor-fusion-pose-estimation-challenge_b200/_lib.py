@@ -81,9 +81,9 @@ SIGNATURES = {
     "sfpe_find_bbox_3d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_void_p,
                                     C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_double,
                                     C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
-                                    C.c_void_p, C.c_void_p, C.c_void_p]),
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sfpe_find_obstacle": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
-                                     C.c_void_p, C.c_void_p, C.c_void_p]),
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sfpe_launch_count": (C.c_int64, [C.c_void_p]),
     "sfpe_last_path": (C.c_char_p, [C.c_void_p]),
     "sfpe_phase_profile": (C.c_int, [C.c_void_p, C.c_int32]),

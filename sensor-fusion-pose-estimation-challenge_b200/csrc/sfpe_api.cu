@@ -497,7 +497,7 @@ extern "C" int sfpe_find_bbox_3d(sfpe_ctx* c, const void* d_distance, const void
                                  int32_t height, int32_t width, const int32_t* d_bbox2d, const double* d_centroid3d,
                                  double x_min, double y_min, double res_rad_h, double res_rad_v, double* d_boxes,
                                  int32_t* d_counts, int64_t cap, double* d_out_pred, double* d_out_box, int32_t* d_n_boxes,
-                                 void* stream) {
+                                 const uint32_t* d_posbits, void* stream) {
   if (!c || n < 0 || height <= 0 || width <= 0 || pix_stride < 1 || frame_stride < 0 || cap < 0) return SFPE_ERR_INVALID_ARG;
   if ((dtype != SFPE_F32 && dtype != SFPE_F64) || (pred_dtype != SFPE_F32 && pred_dtype != SFPE_F64)) return SFPE_ERR_INVALID_ARG;
   if (n > 0 && (!d_distance || !d_height || !d_pred || !d_bbox2d || !d_centroid3d || !d_out_pred || !d_out_box || !d_n_boxes ||
@@ -508,18 +508,19 @@ extern "C" int sfpe_find_bbox_3d(sfpe_ctx* c, const void* d_distance, const void
   CK(c, cudaSetDevice(c->device));
   CK(c, launch_find_bbox_3d(d_distance, d_height, dtype, frame_stride, pix_stride, d_pred, pred_dtype, n, height, width,
                             d_bbox2d, d_centroid3d, x_min, y_min, res_rad_h, res_rad_v, d_boxes, d_counts, cap, d_out_pred,
-                            d_out_box, d_n_boxes, (cudaStream_t)stream, &c->launches));
+                            d_out_box, d_n_boxes, d_posbits, (cudaStream_t)stream, &c->launches));
   return SFPE_OK;
 }
 
 extern "C" int sfpe_find_obstacle(sfpe_ctx* c, const void* d_pred, int32_t pred_dtype, int32_t n_channels, int64_t n,
-                                  int32_t height, int32_t width, int32_t* d_scratch, int32_t* d_out, void* stream) {
+                                  int32_t height, int32_t width, int32_t* d_scratch, int32_t* d_out, uint32_t* d_posbits,
+                                  void* stream) {
   if (!c || n < 0 || height <= 0 || width <= 0 || n_channels < 2) return SFPE_ERR_INVALID_ARG;
   if (pred_dtype != SFPE_F32 && pred_dtype != SFPE_F64) return SFPE_ERR_INVALID_ARG;
   if (n > 0 && (!d_pred || !d_scratch || !d_out)) return SFPE_ERR_INVALID_ARG;
-  if (2ll * height * width > 220 * 1024 || n > 0x7fffffffll) return SFPE_ERR_UNSUPPORTED;   // flags live in shared memory
+  if (9ll * height * width / 8 > 220 * 1024 || n > 0x7fffffffll) return SFPE_ERR_UNSUPPORTED;   // flags live in shared memory
   CK(c, cudaSetDevice(c->device));
-  CK(c, launch_find_obstacle(d_pred, pred_dtype, n_channels, n, height, width, d_scratch, d_out, (cudaStream_t)stream,
+  CK(c, launch_find_obstacle(d_pred, pred_dtype, n_channels, n, height, width, d_scratch, d_out, d_posbits, (cudaStream_t)stream,
                              &c->launches));
   return SFPE_OK;
 }

@@ -70,10 +70,10 @@ cudaError_t launch_find_bbox_3d(const void* distance, const void* height, int dt
                                 const void* y_pred, int pred_dtype, long long n, int H, int W, const int* bbox2d,
                                 const double* centroid3d, double x_min, double y_min, double res_h, double res_v,
                                 double* boxes, int* counts, long long cap, double* out_pred, double* out_box, int* n_boxes,
-                                cudaStream_t st, long long* launches);
+                                const unsigned* posbits, cudaStream_t st, long long* launches);
 
 cudaError_t launch_find_obstacle(const void* y_pred, int pred_dtype, int n_ch, long long n, int H, int W, int* scratch,
-                                 int* out, cudaStream_t st, long long* launches);
+                                 int* out, unsigned* posbits_out, cudaStream_t st, long long* launches);
 
 // fused one-sweep-per-SM path -- sfpe_fused.cu
 struct FusedScratch {

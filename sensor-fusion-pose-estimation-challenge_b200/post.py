@@ -170,7 +170,8 @@ def back_project_2D_2_3D(centroids, bboxes, distance_data, height_data):
     return xyz.cpu().numpy()
 
 
-def find_bbox_3d_device(y_pred, bbox_2d, centroid_3d, range_scan=None, distance=None, height=None, cap=None, stream=None):
+def find_bbox_3d_device(y_pred, bbox_2d, centroid_3d, range_scan=None, distance=None, height=None, cap=None, stream=None,
+                        posbits=None):
     """Device form of find_bbox_3d for a batch.  y_pred (B, H*W, 26) float32/float64 CUDA tensor; bbox_2d (B,4)
     int32 [left, top, right, bottom]; centroid_3d (B,3) float64; images as in back_project_device.  Returns
     (pred (B,7) float64, box (B,8,3) float64, n_boxes (B,) int32) device tensors; n_boxes 0 = the reference's
@@ -210,7 +211,8 @@ def find_bbox_3d_device(y_pred, bbox_2d, centroid_3d, range_scan=None, distance=
         _dtype_code(y_pred), B, H, W, C.c_void_p(bbox_2d.data_ptr()), C.c_void_p(centroid_3d.data_ptr()),
         float(G.X_MIN), float(G.Y_MIN), float(G.RES_RAD[1]), float(G.RES_RAD[0]), C.c_void_p(boxes.data_ptr()),
         C.c_void_p(counts.data_ptr()), cap, C.c_void_p(pred.data_ptr()), C.c_void_p(box.data_ptr()),
-        C.c_void_p(n_boxes.data_ptr()), _stream_ptr(stream))
+        C.c_void_p(n_boxes.data_ptr()), C.c_void_p(posbits.data_ptr()) if posbits is not None else None,
+        _stream_ptr(stream))
     _lib.check(rc, pr._ctx)
     _release_on(stream, boxes, counts)
     return pred, box, n_boxes
@@ -240,7 +242,7 @@ def find_bbox_3d(distance_img, height_img, y_pred, bbox_2d, centroid_3d):
     return pred[0].cpu().numpy(), box[0].cpu().numpy()
 
 
-def find_obstacle_device(y_pred, height, width, stream=None):
+def find_obstacle_device(y_pred, height, width, stream=None, posbits=None):
     """Device form of find_obstacle for a batch: y_pred (B, height*width, n_channels) float32/float64 CUDA tensor.
     Returns an int32 device tensor (B, 8): found, centroid x, y, box left, top, right, bottom, area."""
     torch = _torch()
@@ -252,7 +254,8 @@ def find_obstacle_device(y_pred, height, width, stream=None):
     out = torch.empty((B, 8), dtype=torch.int32, device=y_pred.device)
     pr = _projector(y_pred.device)
     rc = pr.lib.sfpe_find_obstacle(pr._ctx, C.c_void_p(y_pred.data_ptr()), _dtype_code(y_pred), y_pred.shape[2], B, height,
-                                   width, C.c_void_p(scratch.data_ptr()), C.c_void_p(out.data_ptr()), _stream_ptr(stream))
+                                   width, C.c_void_p(scratch.data_ptr()), C.c_void_p(out.data_ptr()),
+                                   C.c_void_p(posbits.data_ptr()) if posbits is not None else None, _stream_ptr(stream))
     _lib.check(rc, pr._ctx)
     _release_on(stream, scratch)
     return out
@@ -282,12 +285,14 @@ def locate_obstacles(prediction, range_scan, stream=None):
     (the reference returns [0,0,0,0] or zeros(7) there)."""
     torch = _torch()
     B, H, W, _ = range_scan.shape
-    obs = find_obstacle_device(prediction, H, W, stream=stream)
+    posbits = torch.empty((B, (H * W + 31) // 32), dtype=torch.int32, device=range_scan.device)   # one pass over the tensor
+    obs = find_obstacle_device(prediction, H, W, stream=stream, posbits=posbits)
     centroids = obs[:, 1:3].to(torch.float64).contiguous()
     bboxes = obs[:, 3:7].to(torch.float64).contiguous()
     xyz, _ = back_project_device(centroids, bboxes, range_scan=range_scan, stream=stream)
     pred, _, n_boxes = find_bbox_3d_device(prediction, obs[:, 3:7].contiguous(), xyz[:, :3].contiguous(),
-                                           range_scan=range_scan, stream=stream)
+                                           range_scan=range_scan, stream=stream, posbits=posbits)
+    _release_on(stream, posbits)
     found = (obs[:, 0] != 0) & ~((xyz[:, 0] == 0) & (xyz[:, 1] == 0)) & (n_boxes > 0)      # :349, :358, :137
     return torch.where(found[:, None], pred, torch.zeros_like(pred)), found
 
