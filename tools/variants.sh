@@ -5,15 +5,15 @@
 set -e
 cd "$(dirname "$0")/../sensor-fusion-pose-estimation-challenge_b200/csrc"
 mkdir -p ../../gpurun_variants
-cp sfpe_fused.cu /tmp/sfpe_fused.orig.cu
+cp sfpe_fused.cu ../../gpurun_variants/.sfpe_fused.orig.cu
 while [ $# -ge 2 ]; do
   name=$1; expr=$2; shift 2
-  cp /tmp/sfpe_fused.orig.cu sfpe_fused.cu
+  cp ../../gpurun_variants/.sfpe_fused.orig.cu sfpe_fused.cu
   sed -i "$expr" sfpe_fused.cu
-  if cmp -s sfpe_fused.cu /tmp/sfpe_fused.orig.cu && [ "$name" != base ]; then echo "variant $name: sed changed nothing"; fi
-  make -j4 > /dev/null 2>&1 || { echo "variant $name: build failed"; cp /tmp/sfpe_fused.orig.cu sfpe_fused.cu; continue; }
+  if cmp -s sfpe_fused.cu ../../gpurun_variants/.sfpe_fused.orig.cu && [ "$name" != base ]; then echo "variant $name: sed changed nothing"; fi
+  make -j4 > /dev/null 2>&1 || { echo "variant $name: build failed"; cp ../../gpurun_variants/.sfpe_fused.orig.cu sfpe_fused.cu; continue; }
   cp ../libsfpe.so ../../gpurun_variants/$name.so
   echo "variant $name: $(grep -A3 k_fused sfpe_fused.o.ptxas.log | grep -E 'Used' | tr -s ' ')"
 done
-cp /tmp/sfpe_fused.orig.cu sfpe_fused.cu
+cp ../../gpurun_variants/.sfpe_fused.orig.cu sfpe_fused.cu
 make -j4 > /dev/null 2>&1
