@@ -300,27 +300,41 @@ def run_ours(a):
 
 
 def run_e2e(a, pkg, pr, pin_in, dev, world):
-    """Host pinned in -> H2D -> kernels -> D2H of every output image, pipelined over chunks on 3 streams."""
+    """Host pinned in -> H2D -> kernels -> D2H of every output image, pipelined over chunks on 3 streams.
+    Both BEV transports are timed (the host ends with the same float images either way); the line's value
+    is the faster one and the note names it."""
+    import gc
     import torch
     import torch.distributed as dist
-    hb = pkg.HostBatchPipeline(pr, a.sweeps, a.n_pts, chunk=a.e2e_chunk)
     steps = max(2, min(a.steps, 5))
-    hb.run(pin_in)            # warm-up (also faults the pinned output pages in)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        hb.run(pin_in)
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
-    t = torch.tensor([dt], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dt = float(t.item())
-    return {"value": world * a.sweeps * steps / dt, "unit": "sweeps/s", "steps": steps,
-            "h2d_bytes_per_step": int(hb.h2d_bytes), "d2h_bytes_per_step": int(hb.d2h_bytes),
-            "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; PCIe bound" % hb.chunk}
+    res = {}
+    for transport in ("dense", "u8"):
+        hb = pkg.HostBatchPipeline(pr, a.sweeps, a.n_pts, chunk=a.e2e_chunk, bev_transport=transport)
+        hb.run(pin_in)            # warm-up (also faults the pinned output pages in)
+        hb.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            hb.run(pin_in)
+        hb.synchronize()
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        res[transport] = {"value": world * a.sweeps * steps / dt, "h2d": int(hb.h2d_bytes), "d2h": int(hb.d2h_bytes),
+                          "chunk": hb.chunk}
+        del hb
+        gc.collect()
+    best = max(res, key=lambda k: res[k]["value"])
+    r = res[best]
+    return {"value": r["value"], "unit": "sweeps/s", "steps": steps,
+            "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"], "bev_transport": best,
+            "by_transport": {k: round(v["value"], 1) for k, v in res.items()},
+            "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; dense: float BEV over PCIe; "
+                    "u8: one byte per BEV cell over PCIe, expanded into the same pinned float image by host "
+                    "threads inside the timed region (bit-identical result)" % r["chunk"]}
 
 
 _JSON_FD = None

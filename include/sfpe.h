@@ -197,6 +197,23 @@ SFPE_API int sfpe_invariant_mask_update(sfpe_ctx* ctx, const void* d_ref, const 
 SFPE_API int sfpe_roll_width(sfpe_ctx* ctx, const void* d_in, void* d_out, int64_t n_frames, int32_t height,
                     int32_t width, int32_t pix_bytes, const int32_t* d_shift, void* stream);
 
+/* ---- compact transport of the BEV density image to a host consumer -----------------------------
+ * The reference keeps every rendered image on the host (process/extract_rosbag.py:162-187).  The
+ * density image of common/birds_eye_view_generator.py:31-37 takes 64 distinct values
+ * (255*min(ln(N+1)/ln 64, 1), N = 0..63, and 255 beyond), so a batch can cross PCIe as one byte per
+ * cell and be rebuilt on the host bit for bit:
+ *   sfpe_density_lut      copies the table the kernels use (65 doubles, [64] = the saturated value);
+ *   sfpe_bev_pack_u8      d_codes[i] = class of d_bev[i] (exact comparison against that table, cast to
+ *                         the image's dtype); *d_flag (device int32, zeroed by the caller) is set to 1
+ *                         if a value is not in the table.  d_bev 16-byte, d_codes 4-byte aligned;
+ *   sfpe_bev_unpack_host  h_out[i] = (dtype) h_lut65[min(h_codes[i], 64)] on n_threads host threads
+ *                         (<= 0: all cores), non-temporal stores.  Needs no context and no GPU. */
+SFPE_API int sfpe_density_lut(sfpe_ctx* ctx, double* h_lut65);
+SFPE_API int sfpe_bev_pack_u8(sfpe_ctx* ctx, const void* d_bev, int32_t dtype, int64_t n_cells, uint8_t* d_codes,
+                     int32_t* d_flag, void* stream);
+SFPE_API int sfpe_bev_unpack_host(const uint8_t* h_codes, int64_t n_cells, const double* h_lut65, void* h_out,
+                         int32_t dtype, int32_t n_threads);
+
 /* Back-projection of cluster centroids (train/predict.py:230-293, back_project_2D_2_3D).  Per item i:
  * if the pixel under the centroid is not valid (distance > 0 and height > min_height) and the box
  * has non-zero left/right, the centroid moves to the valid pixel of the box nearest to it (first in

@@ -478,6 +478,35 @@ extern "C" int sfpe_roll_width(sfpe_ctx* c, const void* d_in, void* d_out, int64
   return SFPE_OK;
 }
 
+extern "C" int sfpe_density_lut(sfpe_ctx* c, double* h_lut65) {
+  if (!c || !h_lut65) return SFPE_ERR_INVALID_ARG;
+  CK(c, cudaSetDevice(c->device));
+  CK(c, cudaStreamSynchronize(c->stream));   // the table is filled on the context's stream at creation
+  CK(c, cudaMemcpy(h_lut65, c->d_lut, 65 * sizeof(double), cudaMemcpyDeviceToHost));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_bev_pack_u8(sfpe_ctx* c, const void* d_bev, int32_t dtype, int64_t n_cells, uint8_t* d_codes,
+                                int32_t* d_flag, void* stream) {
+  if (!c || n_cells < 0 || (dtype != SFPE_F32 && dtype != SFPE_F64)) return SFPE_ERR_INVALID_ARG;
+  if (n_cells > 0 && (!d_bev || !d_codes || !d_flag)) return SFPE_ERR_INVALID_ARG;
+  if (((uintptr_t)d_bev % 16) || ((uintptr_t)d_codes % 4)) return SFPE_ERR_INVALID_ARG;
+  CK(c, cudaSetDevice(c->device));
+  int sms = 0;
+  CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+  CK(c, launch_bev_pack_u8(d_bev, dtype, n_cells, c->d_lut, d_codes, d_flag, sms, (cudaStream_t)stream, &c->launches));
+  return SFPE_OK;
+}
+
+extern "C" int sfpe_bev_unpack_host(const uint8_t* h_codes, int64_t n_cells, const double* h_lut65, void* h_out,
+                                    int32_t dtype, int32_t n_threads) {
+  if (n_cells < 0 || (dtype != SFPE_F32 && dtype != SFPE_F64)) return SFPE_ERR_INVALID_ARG;
+  if (n_cells > 0 && (!h_codes || !h_lut65 || !h_out)) return SFPE_ERR_INVALID_ARG;
+  if ((uintptr_t)h_out % (dtype == SFPE_F32 ? 4 : 8)) return SFPE_ERR_INVALID_ARG;
+  bev_unpack_host(h_codes, n_cells, h_lut65, h_out, dtype, n_threads);
+  return SFPE_OK;
+}
+
 extern "C" int sfpe_back_project(sfpe_ctx* c, double* d_centroids, double* d_bboxes, int64_t n, const void* d_distance,
                                  const void* d_height, int32_t dtype, int64_t frame_stride, int32_t pix_stride,
                                  int32_t height, int32_t width, double min_height, double x_min, double res_rad,

@@ -93,6 +93,11 @@ int fused_grid(int device, int n_frames);
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
                          const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches);
 
+// sfpe_transport.cu: one-byte-per-cell transport of the BEV density image
+cudaError_t launch_bev_pack_u8(const void* bev, int dtype, long long n, const double* lut, unsigned char* codes, int* bad,
+                               int sm_count, cudaStream_t st, long long* launches);
+void bev_unpack_host(const unsigned char* codes, long long n, const double* lut65, void* out, int dtype, int n_threads);
+
 cudaError_t launch_selftest_fastpath(const DevGrid& g, const float* pts, long long n, unsigned long long* d_out4,
                                      cudaStream_t st, long long* launches);
 

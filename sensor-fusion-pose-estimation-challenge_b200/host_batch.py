@@ -6,12 +6,22 @@ chunks that flow through three CUDA streams -- H2D copy, kernels, D2H copy -- wi
 device slots, so both PCIe directions and the SMs work concurrently.  torch is used for
 pinned/device memory, streams and events only.
 """
+from concurrent.futures import ThreadPoolExecutor
+
+from . import _lib
 from .projector import LidarProjector
 
 
 class HostBatchPipeline:
-    def __init__(self, projector: LidarProjector, n_frames, points_per_frame, chunk=32):
+    def __init__(self, projector: LidarProjector, n_frames, points_per_frame, chunk=32, bev_transport="dense",
+                 unpack_threads=0):
+        """bev_transport "dense": the float BEV crosses PCIe as it is (4 bytes per cell).
+        "u8": one byte per cell (sfpe_bev_pack_u8 on the device after the projection), expanded into
+        the same pinned float image by host threads while later chunks are in flight
+        (sfpe_bev_unpack_host) -- the host image is bit-identical, the D2H volume 3x smaller."""
         import torch
+        if bev_transport not in ("dense", "u8"):
+            raise ValueError("bev_transport must be 'dense' or 'u8'")
         self.torch = torch
         self.pr = projector
         self.n_frames, self.n = int(n_frames), int(points_per_frame)
@@ -27,16 +37,45 @@ class HostBatchPipeline:
         self.h_bev = torch.empty((self.n_frames, p.nbx, p.nby), dtype=torch.float32).pin_memory() \
             if p.params.enable_bev else None
         self.h_status = torch.empty((self.n_frames,), dtype=torch.int32).pin_memory()
+        self.u8 = bev_transport == "u8" and self.h_bev is not None
+        self.cells = p.nbx * p.nby
+        self._fut = []
+        if self.u8:
+            self.d_codes = [torch.empty((self.chunk, p.nbx, p.nby), dtype=torch.uint8, device=dev) for _ in range(2)]
+            self.d_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.h_codes = torch.empty((self.n_frames, p.nbx, p.nby), dtype=torch.uint8).pin_memory()
+            self.lut = projector.density_lut()
+            self.unpack_threads = int(unpack_threads)
+            self._pool = ThreadPoolExecutor(max_workers=1)
+            self._unpack = projector.lib.sfpe_bev_unpack_host
         self.h2d_bytes = self.n_frames * self.n * 16
-        self.d2h_bytes = (self.h_range.numel() * 4 if self.h_range is not None else 0) + \
-                         (self.h_bev.numel() * 4 if self.h_bev is not None else 0) + self.n_frames * 4
+        bev_bytes = 0 if self.h_bev is None else self.h_bev.numel() * (1 if self.u8 else 4)
+        self.d2h_bytes = (self.h_range.numel() * 4 if self.h_range is not None else 0) + bev_bytes + self.n_frames * 4
+
+    def _expand(self, ev, f0, nf):
+        """Worker thread: wait for the chunk's D2H, then rebuild its float images in h_bev."""
+        ev.synchronize()
+        n = nf * self.cells
+        _lib.check(self._unpack(self.h_codes.data_ptr() + f0 * self.cells, n, self.lut.ctypes.data,
+                                self.h_bev.data_ptr() + f0 * self.cells * 4, _lib.SFPE_F32, self.unpack_threads))
+
+    def synchronize(self):
+        """Everything of the runs issued so far is in the pinned host outputs."""
+        for f in self._fut:
+            if f is not None:
+                f.result()
+        self.torch.cuda.synchronize(self.dev)
+        if self.u8 and int(self.d_flag.item()) != 0:
+            raise RuntimeError("sfpe_bev_pack_u8 met a value that is not a density value")
 
     def run(self, pinned_points):
         """pinned_points: pinned CPU float32 tensor (n_frames*n, 4).  Asynchronous; results are in
-        self.h_range / self.h_bev / self.h_status after torch.cuda.synchronize()."""
+        self.h_range / self.h_bev / self.h_status after self.synchronize()."""
         torch = self.torch
         ev_in = [None, None]; ev_k = [None, None]; ev_out = [None, None]
         n_chunks = (self.n_frames + self.chunk - 1) // self.chunk
+        if len(self._fut) != n_chunks:
+            self._fut = [None] * n_chunks
         for c in range(n_chunks):
             s = c & 1
             f0 = c * self.chunk
@@ -52,14 +91,23 @@ class HostBatchPipeline:
                     self.s_k.wait_event(ev_out[s])           # D2H of chunk c-2 is done with d_out[s]
                 self.pr.project(self.d_in[s], n_frames=nf, uniform_n=self.n, out=self.d_out[s],
                                 stream=self.s_k.cuda_stream)
+                if self.u8:
+                    self.pr.pack_bev_u8(self.d_out[s]["bev"][:nf], codes=self.d_codes[s][:nf], flag=self.d_flag,
+                                        stream=self.s_k.cuda_stream)
                 ev_k[s] = torch.cuda.Event(); ev_k[s].record(self.s_k)
             with torch.cuda.stream(self.s_out):
                 self.s_out.wait_event(ev_k[s])
                 o = self.d_out[s]
                 if self.h_range is not None:
                     self.h_range[f0:f0 + nf].copy_(o["range"][:nf], non_blocking=True)
-                if self.h_bev is not None:
+                if self.u8:
+                    if self._fut[c] is not None:
+                        self._fut[c].result()                # the previous run's expansion has read h_codes[f0:]
+                    self.h_codes[f0:f0 + nf].copy_(self.d_codes[s][:nf], non_blocking=True)
+                elif self.h_bev is not None:
                     self.h_bev[f0:f0 + nf].copy_(o["bev"][:nf], non_blocking=True)
                 self.h_status[f0:f0 + nf].copy_(o["status"][:nf], non_blocking=True)
                 ev_out[s] = torch.cuda.Event(); ev_out[s].record(self.s_out)
+                if self.u8:
+                    self._fut[c] = self._pool.submit(self._expand, ev_out[s], f0, nf)
         return self

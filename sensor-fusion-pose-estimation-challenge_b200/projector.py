@@ -216,6 +216,34 @@ class LidarProjector:
         _lib.check(rc, self._ctx)
         return out
 
+    # ------------------------------------------------------------------ one-byte BEV transport (host consumers)
+    def density_lut(self):
+        """The 65 density values the kernels write (birds_eye_view_generator.py:31-37), as float64."""
+        lut = np.empty(65, dtype=np.float64)
+        _lib.check(self.lib.sfpe_density_lut(self._ctx, lut.ctypes.data), self._ctx)
+        return lut
+
+    def pack_bev_u8(self, bev, codes=None, flag=None, stream=None):
+        """bev: contiguous CUDA float32/float64 density image(s) written by project().  Returns
+        (codes, flag): uint8 class per cell and a device int32 that becomes 1 if a value is not a
+        density value.  unpack_bev_host(codes.cpu(), ...) gives the image back bit for bit."""
+        torch = _torch()
+        if not bev.is_cuda or bev.device.index != self.device or not bev.is_contiguous():
+            raise ValueError("bev must be a contiguous CUDA tensor on cuda:%d" % self.device)
+        if bev.dtype not in (torch.float32, torch.float64):
+            raise ValueError("bev must be float32 or float64")
+        if codes is None:
+            codes = torch.empty(bev.shape, dtype=torch.uint8, device=bev.device)
+        if flag is None:
+            flag = torch.zeros(1, dtype=torch.int32, device=bev.device)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        dt = _lib.SFPE_F32 if bev.dtype == torch.float32 else _lib.SFPE_F64
+        rc = self.lib.sfpe_bev_pack_u8(self._ctx, bev.data_ptr(), dt, int(bev.numel()), codes.data_ptr(), flag.data_ptr(),
+                                       C.c_void_p(int(stream)))
+        _lib.check(rc, self._ctx)
+        return codes, flag
+
     # ------------------------------------------------------------------ one sweep, host in / host out
     def project_sweep_host(self, points, columns=(0, 1, 2, 3), range_dtype=np.float64, range_layout="chw",
                            bev_dtype=np.float64, want_range=True, want_bev=True, want_winner=False):
@@ -251,3 +279,21 @@ class LidarProjector:
             C.byref(st), C.byref(dr))
         _lib.check(rc, self._ctx)
         return rng, win, bev, st.value, dr.value
+
+
+
+def unpack_bev_host(codes, lut, out=None, dtype=np.float32, threads=0):
+    """Host side of the one-byte BEV transport: out[i] = dtype(lut[codes[i]]) on `threads` host
+    threads (0: all cores).  codes: C-contiguous uint8 array; lut: LidarProjector.density_lut()."""
+    lib = _lib.load()
+    codes = np.ascontiguousarray(codes, dtype=np.uint8)
+    lut = np.ascontiguousarray(lut, dtype=np.float64)
+    if lut.size != 65:
+        raise ValueError("lut must hold 65 values")
+    if out is None:
+        out = np.empty(codes.shape, dtype=dtype)
+    if out.size != codes.size or not out.flags.c_contiguous or out.dtype not in (np.float32, np.float64):
+        raise ValueError("out must be a C-contiguous float32/float64 array of codes.size elements")
+    dt = _lib.SFPE_F32 if out.dtype == np.float32 else _lib.SFPE_F64
+    _lib.check(lib.sfpe_bev_unpack_host(codes.ctypes.data, int(codes.size), lut.ctypes.data, out.ctypes.data, dt, int(threads)))
+    return out

@@ -82,3 +82,24 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 txt = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in txt and "from oracle" not in txt, f
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_bev_unpack_host_is_a_table_lookup(dtype):
+    """Host half of the one-byte BEV transport (needs no GPU): out[i] = dtype(lut[code[i]]), any
+    alignment, any length, neighbours untouched; the table is the reference's normalize()
+    (common/birds_eye_view_generator.py:31-37)."""
+    proj = load_sub("projector")
+    lut = np.array([0.0] + [255.0 * min(np.log(n + 1.0) / np.log(64.0), 1.0) for n in range(1, 65)])
+    rng = np.random.default_rng(5)
+    for n in [0, 1, 15, 16, 17, 63, 64, 65, 4097, 300000]:
+        codes = rng.integers(0, 64, n).astype(np.uint8)
+        codes[rng.random(n) < 0.9] = 0
+        for threads in (0, 1, 3):
+            buf = np.full(n + 7, -7, dtype)
+            out = buf[3:3 + n]
+            proj.unpack_bev_host(codes, lut, out=out, threads=threads)
+            assert np.array_equal(out, lut[codes].astype(dtype))
+            assert (buf[:3] == -7).all() and (buf[3 + n:] == -7).all()
+    with pytest.raises(ValueError):
+        proj.unpack_bev_host(np.zeros(4, np.uint8), lut[:10])

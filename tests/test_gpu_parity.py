@@ -414,3 +414,66 @@ def test_fused_equals_generic_randomized(pkg, synth, seed):
     assert a["_path"] == "fused" and b["_path"] == "generic"
     for k in ("range", "winner", "bev", "status", "dropped"):
         assert np.array_equal(a[k], b[k]), k
+
+
+@pytest.mark.parametrize("bev_dtype", ["f32", "f64"])
+def test_bev_u8_transport_round_trip(pkg, synth, bev_dtype):
+    """sfpe_bev_pack_u8 + sfpe_bev_unpack_host rebuild the density image bit for bit (saturated cells
+    included), the class IS min(count, 63) of the oracle, and a foreign value raises the flag."""
+    import importlib
+    import torch
+    proj = importlib.import_module(pkg.__name__ + ".projector")
+    frames = [synth.make_sweep("hdl32", seed=21), synth.make_sweep("hdl64", seed=22, n_az=300)]
+    dense = np.zeros((4000, 4), np.float32)          # 4000 points in a handful of cells: counts >= 63
+    dense[:, 0] = 10.0 + 0.3 * np.random.default_rng(3).random(4000)
+    dense[:, 1] = -5.0
+    dense[:, 2] = -1.0
+    frames.append(dense)
+    pr = pkg.LidarProjector(device=0, bev_res=(0.2, 0.2))
+    pts = torch.from_numpy(np.concatenate(frames)).cuda()
+    offs = np.zeros(len(frames) + 1, np.int64)
+    offs[1:] = np.cumsum([len(f) for f in frames])
+    out = pr.alloc_outputs(len(frames), bev_dtype=bev_dtype)
+    pr.project(pts, n_frames=len(frames), frame_offsets=torch.from_numpy(offs).cuda(),
+               max_n=max(len(f) for f in frames), out=out)
+    codes, flag = pr.pack_bev_u8(out["bev"])
+    torch.cuda.synchronize()
+    assert int(flag.item()) == 0
+    lut = pr.density_lut()
+    np_dt = np.float32 if bev_dtype == "f32" else np.float64
+    back = proj.unpack_bev_host(codes.cpu().numpy(), lut, dtype=np_dt)
+    bev = out["bev"].cpu().numpy()
+    assert back.dtype == bev.dtype and np.array_equal(back, bev)
+    assert codes.max().item() == 63
+    for f, p in enumerate(frames):
+        counts = lo.bev_counts(p.astype(np.float64), (0.2, 0.2))
+        assert np.array_equal(codes[f].cpu().numpy(), np.minimum(counts, 63)[::-1, ::-1].astype(np.uint8))
+    bad = out["bev"].clone()
+    bad.view(-1)[12345] = 1.0                         # not a density value
+    _, flag = pr.pack_bev_u8(bad)
+    assert int(flag.item()) == 1
+    pr.close()
+
+
+@pytest.mark.parametrize("transport", ["dense", "u8"])
+def test_host_batch_pipeline_matches_device_batch(pkg, synth, transport):
+    """HostBatchPipeline (pinned host in -> pinned host out, ragged last chunk, run twice) delivers the
+    images of one device-resident project() call, whichever way the BEV crosses PCIe."""
+    import torch
+    n_frames, n = 7, 65536
+    host = np.concatenate([synth.make_sweep("hdl32", seed=40 + i) for i in range(n_frames)])
+    assert host.shape == (n_frames * n, 4)
+    pin = torch.from_numpy(host).pin_memory()
+    pr = pkg.LidarProjector(device=0, bev_res=(0.2, 0.2))
+    ref = pr.alloc_outputs(n_frames)
+    pr.project(pin.cuda(), n_frames=n_frames, uniform_n=n, out=ref)
+    hb = pkg.HostBatchPipeline(pr, n_frames, n, chunk=3, bev_transport=transport)
+    hb.h_bev.fill_(-1.0)
+    hb.run(pin)
+    hb.run(pin)
+    hb.synchronize()
+    assert np.array_equal(hb.h_range.numpy(), ref["range"].cpu().numpy())
+    assert np.array_equal(hb.h_bev.numpy(), ref["bev"].cpu().numpy())
+    assert np.array_equal(hb.h_status.numpy(), ref["status"].cpu().numpy())
+    assert hb.d2h_bytes == n_frames * (32 * 1801 * 3 * 4 + pr.nbx * pr.nby * (1 if transport == "u8" else 4) + 4)
+    pr.close()
