@@ -14,7 +14,7 @@ from .projector import LidarProjector
 
 class HostBatchPipeline:
     def __init__(self, projector: LidarProjector, n_frames, points_per_frame, chunk=32, bev_transport="dense",
-                 unpack_threads=0):
+                 unpack_threads=0, unpack_workers=2):
         """bev_transport "dense": the float BEV crosses PCIe as it is (4 bytes per cell).
         "u8": one byte per cell (sfpe_bev_pack_u8 on the device after the projection), expanded into
         the same pinned float image by host threads while later chunks are in flight
@@ -45,8 +45,12 @@ class HostBatchPipeline:
             self.d_flag = torch.zeros(1, dtype=torch.int32, device=dev)
             self.h_codes = torch.empty((self.n_frames, p.nbx, p.nby), dtype=torch.uint8).pin_memory()
             self.lut = projector.density_lut()
-            self.unpack_threads = int(unpack_threads)
-            self._pool = ThreadPoolExecutor(max_workers=1)
+            # two chunks expand side by side (one worker waits for its copy while the other writes); the
+            # cores are split between them.  Measured on the B200 box (16 cores): host DRAM is the limit.
+            import os
+            workers = max(1, int(unpack_workers))
+            self.unpack_threads = int(unpack_threads) if unpack_threads > 0 else max(1, (os.cpu_count() or 1) // workers)
+            self._pool = ThreadPoolExecutor(max_workers=max(1, int(unpack_workers)))
             self._unpack = projector.lib.sfpe_bev_unpack_host
         self.h2d_bytes = self.n_frames * self.n * 16
         bev_bytes = 0 if self.h_bev is None else self.h_bev.numel() * (1 if self.u8 else 4)
