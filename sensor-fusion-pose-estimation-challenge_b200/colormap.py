@@ -27,3 +27,23 @@ def to_rgb_bytes(img, cmap, vmin=None, vmax=None):
         out.ctypes.data_as(C.c_void_p))
     _lib.check(rc, pr._ctx)
     return out
+
+
+def device_rgb(pr, img, cmap, vmin=None, vmax=None, stream=None):
+    """CUDA float32/float64 image (any shape, contiguous) -> CUDA uint8 image img.shape + (3,) through
+    sfpe_colormap on `pr`'s context: the float image never leaves the device."""
+    import torch
+    if cmap not in CMAPS:
+        raise ValueError("colormap %r is not available (have: %s)" % (cmap, ", ".join(sorted(CMAPS))))
+    if not img.is_cuda or not img.is_contiguous() or img.dtype not in (torch.float32, torch.float64):
+        raise ValueError("img must be a contiguous CUDA float32/float64 tensor")
+    out = torch.empty(tuple(img.shape) + (3,), dtype=torch.uint8, device=img.device)
+    auto = vmin is None or vmax is None
+    if stream is None:
+        stream = torch.cuda.current_stream(pr.device).cuda_stream
+    rc = pr.lib.sfpe_colormap(
+        pr._ctx, C.c_void_p(img.data_ptr()), _lib.SFPE_F32 if img.dtype == torch.float32 else _lib.SFPE_F64,
+        img.numel(), CMAPS[cmap], int(auto), 0.0 if auto else float(vmin), 0.0 if auto else float(vmax),
+        C.c_void_p(out.data_ptr()), C.c_void_p(int(stream)))
+    _lib.check(rc, pr._ctx)
+    return out

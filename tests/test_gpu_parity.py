@@ -477,3 +477,25 @@ def test_host_batch_pipeline_matches_device_batch(pkg, synth, transport):
     assert np.array_equal(hb.h_status.numpy(), ref["status"].cpu().numpy())
     assert hb.d2h_bytes == n_frames * (32 * 1801 * 3 * 4 + pr.nbx * pr.nby * (1 if transport == "u8" else 4) + 4)
     pr.close()
+
+
+@pytest.mark.parametrize("cmap", ["gray", "jet"])
+def test_generate_birds_eye_view_single_device_pass(pkg, synth, cmap):
+    """generate_birds_eye_view (birds_eye_view_generator.py:41-54) keeps the float image on the device;
+    its bytes are those of the colormap applied to the pinned density image, for every input form the
+    reference's np.array(arrPoints) accepts (float32, float64, two columns, lists, no points)."""
+    import importlib
+    cm = importlib.import_module(pkg.__name__ + ".colormap")
+    p32 = synth.make_sweep("hdl32", seed=77)
+    cases = [p32, p32.astype(np.float64) * 1.0000001, p32[:5000, :2].astype(np.float64), p32[:300, :3].tolist(),
+             np.zeros((0, 4), np.float32)]
+    for res in [(0.2, 0.2), (0.5, 0.25)]:
+        for pts in cases:
+            img = pkg.generate_birds_eye_view(pts, None, res, cmap=cmap)
+            dens = pkg.birds_eye_view_density(pts, res)
+            want = cm.to_rgb_bytes(dens, cmap, vmin=0, vmax=1500 * res[0])
+            assert img.dtype == np.uint8 and img.shape == dens.shape + (3,)
+            assert np.array_equal(img, want)
+    assert pkg.generate_birds_eye_view(p32, None, (0.2, 0.2), cmap="gray").max() > 0
+    with pytest.raises(ValueError):
+        pkg.generate_birds_eye_view(p32, None, (0.2, 0.2), cmap="viridis")
