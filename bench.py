@@ -325,6 +325,7 @@ def run_e2e(a, pkg, pr, pin_in, dev, world):
         dt = float(t.item())
         res[transport] = {"value": world * a.sweeps * steps / dt, "h2d": int(hb.h2d_bytes), "d2h": int(hb.d2h_bytes),
                           "chunk": hb.chunk}
+        hb.close()
         del hb
         gc.collect()
     best = max(res, key=lambda k: res[k]["value"])

@@ -63,6 +63,12 @@ class HostBatchPipeline:
         _lib.check(self._unpack(self.h_codes.data_ptr() + f0 * self.cells, n, self.lut.ctypes.data,
                                 self.h_bev.data_ptr() + f0 * self.cells * 4, _lib.SFPE_F32, self.unpack_threads))
 
+    def close(self):
+        """Stop the expanding workers (after the last synchronize())."""
+        if self.u8 and self._pool is not None:
+            self._pool.shutdown(wait=True)
+            self._pool = None
+
     def synchronize(self):
         """Everything of the runs issued so far is in the pinned host outputs."""
         for f in self._fut:

@@ -476,6 +476,7 @@ def test_host_batch_pipeline_matches_device_batch(pkg, synth, transport):
     assert np.array_equal(hb.h_bev.numpy(), ref["bev"].cpu().numpy())
     assert np.array_equal(hb.h_status.numpy(), ref["status"].cpu().numpy())
     assert hb.d2h_bytes == n_frames * (32 * 1801 * 3 * 4 + pr.nbx * pr.nby * (1 if transport == "u8" else 4) + 4)
+    hb.close()
     pr.close()
 
 
