@@ -100,50 +100,98 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ CPU baseline
+def _cpu_impl():
+    """(kind, front_view(P), bev(P, res, vectorised)).  kind "reference": the reference's own files
+    (process/extract_rosbag_lidar.py, common/birds_eye_view_generator.py, process/globals.py), loaded unmodified
+    through oracle/reference_loader.py from /root/reference or from oracle/_ref (the copy oracle/make_ref.py made
+    at build time, which travels to the GPU box).  kind "port": the op-for-op numpy port, only when neither
+    exists.  The vectorised-normalize variant is always the port (the reference has no such form)."""
+    from oracle import lidar_oracle as lo
+    from oracle import reference_loader as rl
+    vec = lambda P, res: lo.port_generate_birds_eye_view(P, res, 120, python_loop=False)
+    if rl.available():
+        return "reference", rl.front_view, (lambda P, res: rl.bev_density(P, res, 120)), vec
+    return "port", lo.port_generate_lidar_2d_front_view, (lambda P, res: lo.port_generate_birds_eye_view(P, res, 120, python_loop=True)), vec
+
+
 def _cpu_worker(args):
-    """Times the reference's numpy algorithm (oracle port, op for op) on one host core."""
-    seeds, sensor, bev_res = args
-    synth = importlib.import_module(PKG + ".synth") if False else None  # product package needs the .so; avoid
+    """Rasterises its sweeps with the reference's CPU code on one host core; returns (kind, seconds per sweep)."""
+    seeds, sensor, bev_res, vectorised = args
     import importlib.util
-    spec = importlib.util.spec_from_file_location("synth", os.path.join(ROOT, PKG, "synth.py"))
+    spec = importlib.util.spec_from_file_location("synth", os.path.join(ROOT, PKG, "synth.py"))   # the package itself needs the .so
     synth = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(synth)
-    from oracle import lidar_oracle as lo
+    kind, front, bev, bev_vec = _cpu_impl()
     pts = [synth.as_reference_array(synth.make_sweep(sensor, s)) for s in seeds]
-    t0 = time.perf_counter()
+    out = []
     for P in pts:
-        lo.port_generate_lidar_2d_front_view(P)
-        lo.port_generate_birds_eye_view(P, bev_res, 120, python_loop=True)
-    return time.perf_counter() - t0
+        t0 = time.perf_counter()
+        front(P)
+        (bev_vec if vectorised else bev)(P, bev_res)
+        out.append(time.perf_counter() - t0)
+    return kind, out
 
 
 class CpuReference:
-    """The reference's numpy algorithm on all host cores: one persistent pool of worker processes
-    (spawn, each pinned to its own disjoint sweeps).  pass_(n) rasterises n sweeps, returns wall seconds."""
+    """The reference's CPU code on all host cores: one persistent pool of worker processes (spawn), each
+    rasterising its own disjoint sweeps.  pass_(n) rasterises n sweeps and returns wall seconds."""
 
     def __init__(self, sensor, bev_res, cores=None):
         import multiprocessing as mp
         self.cores = cores or os.cpu_count() or 1
         self.sensor, self.bev_res = sensor, bev_res
         self.pool = mp.get_context("spawn").Pool(self.cores)
-        self.pool.map(_cpu_worker, [([i], sensor, bev_res) for i in range(self.cores)])     # imports + warm-up
+        r = self.pool.map(_cpu_worker, [([i], sensor, bev_res, True) for i in range(self.cores)])     # imports + warm-up
+        self.kind = r[0][0]
 
-    def pass_(self, n_sweeps, seed0=0):
+    def pass_(self, n_sweeps, seed0=0, vectorised=False):
         chunks = [list(range(seed0 + i, seed0 + n_sweeps, self.cores)) for i in range(self.cores)]
         chunks = [c for c in chunks if c]
         t0 = time.perf_counter()
-        self.pool.map(_cpu_worker, [(c, self.sensor, self.bev_res) for c in chunks])
+        self.pool.map(_cpu_worker, [(c, self.sensor, self.bev_res, vectorised) for c in chunks])
         return time.perf_counter() - t0
+
+    def single_core(self, n=5, seed0=500, vectorised=False):
+        """n sweeps one after the other in ONE worker process: per-sweep milliseconds (best, median)."""
+        _, t = self.pool.apply(_cpu_worker, ((list(range(seed0, seed0 + n)), self.sensor, self.bev_res, vectorised),))
+        return {"best_of_%d" % n: 1e3 * min(t), "median": 1e3 * float(np.median(t))}
+
+    def describe(self):
+        return ("the reference's own files (extract_rosbag_lidar.py, birds_eye_view_generator.py, globals.py; "
+                "oracle/_ref)" if self.kind == "reference" else "numpy port of the reference (oracle/_ref absent)") + \
+               ": 3x lidar_2d_front_view + histogram2d + per-cell python normalize loop, colormap stubbed"
 
     def close(self):
         self.pool.close()
         self.pool.join()
 
 
+def cpu_baseline_block(a, target_s=15.0):
+    """(i) one core, best of 5 and median per sweep; (ii) all host cores over disjoint sweeps
+    (the headline `value`); and the same two with the python per-cell `normalize` loop replaced by its vectorised
+    equivalent, which shows how much of the CPU time is that loop."""
+    ref = CpuReference(a.sensor, (a.bev_res, a.bev_res))
+    one = ref.single_core(5)
+    one_vec = ref.single_core(5, vectorised=True)
+    n = ref.cores * 2
+    dt = ref.pass_(n)
+    n = int(max(ref.cores * 2, min(4096, n * target_s / max(dt, 1e-3))))
+    dt = ref.pass_(n, seed0=1000)
+    nv = ref.cores * 16
+    dtv = ref.pass_(nv, seed0=3000, vectorised=True)
+    ref.close()
+    return {"value": n / dt, "unit": "sweeps/s", "cores": ref.cores, "kind": ref.kind,
+            "sample": "%d sweeps of the same workload in %d processes (%.1f s); %s" % (n, ref.cores, dt, ref.describe()),
+            "single_core_ms_per_sweep": one,
+            "vectorised_normalize": {"single_core_ms_per_sweep": one_vec, "all_cores_sweeps_per_s": nv / dtv,
+                                     "note": "numpy port with the python normalize loop "
+                                             "(birds_eye_view_generator.py:31-37) replaced by array operations"}}
+
+
 def run_reference(a):
-    """--impl reference: the reference's own CPU algorithm (oracle port; the reference is Python and
-    cannot travel to the GPU box) on all host cores, same metric / config.  Each step is a bounded
-    sample of the workload (4 sweeps per core)."""
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref: its three files,
+    unmodified) on all host cores, same metric / config.  Each step is a bounded sample of the workload
+    (4 sweeps per core)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -155,6 +203,7 @@ def run_reference(a):
         dt = ref.pass_(per_step, seed0=i * per_step)
         if i >= a.warmup:
             times.append(dt)
+    desc = ref.describe()
     ref.close()
     total = sum(times)
     val = per_step * len(times) / total
@@ -165,10 +214,9 @@ def run_reference(a):
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": cfg,
-        "cpu_baseline": {"value": val, "unit": "sweeps/s", "cores": cores, "kind": "port",
-                         "sample": "%d sweeps per step x %d steps of the same workload, numpy port of the reference "
-                                   "(3x front view + histogram2d + per-cell python normalize loop) in %d processes"
-                                   % (per_step, len(times), cores)},
+        "cpu_baseline": {"value": val, "unit": "sweeps/s", "cores": cores, "kind": ref.kind,
+                         "sample": "%d sweeps per step x %d steps of the same workload in %d processes; %s"
+                                   % (per_step, len(times), cores, desc)},
         "e2e": {"value": val, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -230,6 +278,7 @@ def run_ours(a):
         ev[i + 1].record()
     barrier()
     launches = pr.launch_count - l0
+    path_timed = pr.last_path
     total_ms = ev[0].elapsed_time(ev[-1])
     step_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(a.steps)]
     clocks = sampler.stop() if rank == 0 else None
@@ -256,6 +305,14 @@ def run_ours(a):
         phases = {k: round(v / tot, 4) for k, v in cyc.items() if v}
         phases["sm_cycles_per_sweep"] = tot / (2 * a.sweeps)
 
+    # ---- the timed launch is checked: K random frames of the batch are rasterised again by the generic
+    # (global-atomics, fp64) path and must equal the slices of the timed output bit for bit (every rank)
+    verified = verify_frames(a, pkg, path_timed, d_pts, out, local, rank)
+    if world > 1:
+        v = torch.tensor([verified], device=dev, dtype=torch.int64)
+        dist.all_reduce(v, op=dist.ReduceOp.MIN)
+        verified = int(v.item())
+
     status_bad = int((out["status"] != 0).sum().item())
     dropped_mean = float(out["dropped"].float().mean().item()) if "dropped" in out else None
     if rank == 0:
@@ -271,11 +328,12 @@ def run_ours(a):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 decisions proven by guard bands, f64 where unproven (bit-exact with the reference's f64); f32 outputs",
             "data": "synthetic", "config": workload_config(a),
-            "path": pr.last_path, "gpu_launches": int(launches), "frames_with_status": status_bad, "dropped_mean": dropped_mean,
+            "path": path_timed, "gpu_launches": int(launches), "frames_with_status": status_bad, "dropped_mean": dropped_mean,
+            "verified_frames": verified,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": measured_traffic(pr.last_path, a.sweeps), "peak_source": peak_src,
+                         "traffic": measured_traffic(path_timed, a.sweeps), "peak_source": peak_src,
                          "algorithmic_bytes_per_sweep": bytes_sweep, "launch_ms": med_ms,
-                         "kernel": "fused k_fused_sweep (one launch per step)" if pr.last_path == "fused"
+                         "kernel": "fused k_fused_sweep (one launch per step)" if path_timed == "fused"
                          else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
             "clocks": clocks,
         }
@@ -284,19 +342,31 @@ def run_ours(a):
         if e2e is not None:
             line["e2e"] = e2e
         if not a.no_cpu and world == 1:
-            ref = CpuReference(a.sensor, (a.bev_res, a.bev_res))
-            n = ref.cores * 8
-            dt = ref.pass_(n)
-            n = int(max(ref.cores * 8, min(4096, n * 15.0 / max(dt, 1e-3))))     # aim at ~15 s of wall time
-            dt = ref.pass_(n, seed0=1000)
-            ref.close()
-            line["cpu_baseline"] = {"value": n / dt, "unit": "sweeps/s", "cores": ref.cores, "kind": "port",
-                                    "sample": "%d sweeps of the same workload, numpy port of the reference in %d "
-                                              "processes (%.1f s)" % (n, ref.cores, dt)}
+            line["cpu_baseline"] = cpu_baseline_block(a)
         emit(line)
     pr.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def verify_frames(a, pkg, path_timed, d_pts, out, local, rank, k=8):
+    """Returns k when k random frames of the timed output equal the generic path's rasterisation of the same
+    points (range tensor and BEV density, bit for bit); raises otherwise.  0 when the timed path was the
+    generic one itself."""
+    import torch
+    if path_timed != "fused" or a.debug_flags:
+        return 0
+    rng = np.random.default_rng(1234 + rank)
+    frames = sorted(int(f) for f in rng.choice(a.sweeps, size=min(k, a.sweeps), replace=False))
+    chk = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=1)
+    for f in frames:
+        o = chk.project(d_pts[f * a.n_pts:(f + 1) * a.n_pts], n_frames=1, uniform_n=a.n_pts)
+        torch.cuda.synchronize()
+        for key in ("range", "bev", "status", "dropped"):
+            if not torch.equal(o[key][0], out[key][f]):
+                raise RuntimeError("bench: frame %d of the timed output differs from the generic path in %r" % (f, key))
+    chk.close()
+    return len(frames)
 
 
 def run_e2e(a, pkg, pr, pin_in, dev, world):

@@ -1,9 +1,11 @@
 """Import the reference's own hot-path modules, unmodified, from /root/reference.
 
-TEST INFRASTRUCTURE (see oracle/__init__.py).  Works only where the reference tree
-is mounted (the build container); the GPU box has no /root/reference, so nothing
-that runs there may call this.  Used by tests/golden/make_golden.py to generate the
-committed golden vectors and by the `-m "not gpu"` cross-check of the restatement.
+TEST INFRASTRUCTURE (see oracle/__init__.py).  The whole tree is mounted only in the
+build container; the GPU box has no /root/reference, but the three hot-path files
+travel there as oracle/_ref/ (copied unmodified by oracle/make_ref.py, git-ignored).
+Used by tests/golden/make_golden.py to generate the committed golden vectors, by the
+`-m "not gpu"` cross-check of the restatement, and by bench.py's CPU arms (front_view /
+bev_density only -- the train/predict.py helpers below need the full tree).
 
 The reference modules import ROS / matplotlib at module scope
 (modules/lidar/process/extract_rosbag_lidar.py:10-16,
@@ -18,14 +20,31 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("SFPE_REFERENCE_ROOT", "/root/reference")
+def _default_root():
+    """The mounted reference tree (build container) or, where that does not exist (the GPU box), the three
+    hot-path files that oracle/make_ref.py copied unmodified into oracle/_ref/."""
+    env = os.environ.get("SFPE_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isdir("/root/reference/modules/lidar"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _default_root()
 _LIDAR = os.path.join(REFERENCE_ROOT, "modules", "lidar")
 
 _cache = {}
 
 
 def available():
+    """The three hot-path files (front view, BEV, constants) can be loaded."""
     return os.path.isfile(os.path.join(_LIDAR, "process", "extract_rosbag_lidar.py"))
+
+
+def full_tree_available():
+    """train/predict.py is there too (only in the build container, never in oracle/_ref)."""
+    return available() and os.path.isfile(os.path.join(_LIDAR, "train", "predict.py"))
 
 
 class _Capture:

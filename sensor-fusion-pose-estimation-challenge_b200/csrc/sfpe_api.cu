@@ -174,6 +174,7 @@ extern "C" int sfpe_create(int device, const sfpe_params* p, sfpe_ctx** out) {
   }
   CKC(cudaSetDevice(device));
   CKC(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CKC(prepare_fused());
   // chunk: keep the scratch of one chunk L2 resident (126 MB L2; budget 40 MB)
   const size_t pf = per_frame_scratch(g);
   size_t chunk = pf ? (40u << 20) / pf : 1;
@@ -288,13 +289,15 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.per_cta = (max_n + 255) & ~255ll;
     if (fx.per_cta < 256) fx.per_cta = 256;
     const FusedGeom geo = fused_geometry(g);
-    const size_t need = (size_t)fx.grid * fx.per_cta * 4 * (geo.n_buckets + 1 + 12) + 256;   // entry buckets + deferred queue + collision records + claim counter
-    const int grc = grow(c, &c->fused_buf, &c->fused_cap, need);
+    // entry buckets + deferred queue + collision records + parked BEV row bitmaps (two frames) + claim counter
+    const size_t words = (size_t)fx.grid * fx.per_cta * (geo.n_buckets + 1 + 12) + (size_t)fx.grid * geo.rows_cap * 2;
+    const int grc = grow(c, &c->fused_buf, &c->fused_cap, words * 4 + 256);
     if (grc) return grc;
     fx.entries = (unsigned*)c->fused_buf;
     fx.queue = fx.entries + (size_t)fx.grid * fx.per_cta * geo.n_buckets;
     fx.cqueue = fx.queue + (size_t)fx.grid * fx.per_cta;
-    fx.counter = fx.cqueue + (size_t)fx.grid * fx.per_cta * 12;
+    fx.rowbits = fx.cqueue + (size_t)fx.grid * fx.per_cta * 12;
+    fx.counter = fx.rowbits + (size_t)fx.grid * geo.rows_cap * 2;
     fs.frame0 = 0; fs.n_frames = n_frames;
     fx.debug = c->params.reserved[0];
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;

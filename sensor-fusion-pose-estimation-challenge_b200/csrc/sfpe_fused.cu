@@ -1,7 +1,8 @@
 // Fused "one sweep per SM" path (the hot path of bench.py).
 //
-// A persistent CTA (512 threads = 15 compute warps + 1 zero-fill warp, 128 registers, ~227 KB
-// dynamic shared memory, one CTA per SM) claims whole sweeps from a global counter.  Per sweep:
+// A persistent CTA (512 threads = 15 compute warps + 1 store warp, 128 registers, ~227 KB
+// dynamic shared memory, one CTA per SM) claims whole sweeps from a global counter.  Per sweep
+// the compute warps run:
 //   S0  range-scan winner keys (H*W x u32) are initialised in shared memory
 //   S1  point pass, 4 points per thread and iteration in two register sets (the next iteration's
 //       16-byte point loads are in flight while this one is rasterised; L2 prefetch 3 ahead).
@@ -16,16 +17,18 @@
 //       winners (prefetched into L2 two tasks ahead, loaded one task ahead) and writes 48
 //       contiguous bytes per lane with one 32-byte and one 16-byte store
 //   S2  BEV, one flat tile (2^17 cells) of the output at a time: u8 counts composed in shared
-//       memory from the tile's bucket, then each warp lists the non-empty 32-byte sectors of
-//       its part of the tile and writes them with one 32-byte store each over the zero fill
-//   ZF  the zero-fill warp streams the frame's zeros (STG.256), fast while the compute warps are
-//       in S1 / S2-compose (which hardly use the SM's path to L2), slowly while they wait on loads
-//       (S1b, S1d) or store themselves (S1c, S2 write-out), unpaced when they wait for it.
+//       memory from the tile's bucket; the tile is then scanned and PARKED in L2 in compact
+//       form: per 1 KB row of the output (32 sectors of 32 bytes) one bitmap word + the list
+//       position of its first non-empty sector, and the u8 counts of the non-empty sectors only
+// and the store warp writes the BEV image of the sweep the compute warps have just parked --
+// every 32-byte sector exactly once, zeros and values alike, as whole 128-byte-aligned 1 KB rows --
+// while the compute warps rasterise the next sweep: fast while they are in S1 / S2 (which hardly
+// use the SM's path to L2), slowly while they wait on loads (S1b, S1d) or store themselves
+// (S1c), unpaced when they wait for it.  The last sweep of a CTA is written by all 16 warps.
 // What bounds it (profiles/README.md): the SM's port to L2 moves one request (<= 128-byte line)
 // per ~4 cycles whatever its size, so the phases are tuned for few, full requests, and the
-// zero fill's 45 k lines per sweep are placed where the other phases issue the fewest.
-// HBM traffic: points read once (+ the winner gather), range written once, BEV written once plus
-// the non-empty sectors a second time.
+// BEV image's 45 k lines per sweep are placed where the other phases issue the fewest.
+// HBM traffic: points read once (+ the winner gather), range written once, BEV written once.
 #include "sfpe_internal.h"
 
 namespace sfpe {
@@ -35,7 +38,7 @@ constexpr int IDX_BITS32 = 18;                       // point index bits of the 
 constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
-constexpr int SMEM_MISC_WORDS = 256;                 // LUT (65 floats) | 16 counters | 16 profile words | bucket counts
+constexpr int SMEM_MISC_WORDS = 256;                 // LUT (129 floats) | 16 counters | 16 profile words | bucket counts | rings
 constexpr int ENTRY_BATCH = 3;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
@@ -120,8 +123,11 @@ __device__ __forceinline__ bool tile_count(unsigned* tile, unsigned r) {
 // in the tile (>= T: not in this tile); returns (r | TC_VALID | previous byte << 24) or 0.
 // finish: an add on a byte that was already >= 128 is undone, and the >= 192 observation reported.
 constexpr unsigned TC_VALID = 1u << 23;
-__device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned r, unsigned T) {
+// Every counted cell also marks its 128-byte output line (32 cells) in the tile's line flags: one
+// byte per line, plain stores (everybody writes the same 1).
+__device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned char* lf, unsigned r, unsigned T) {
   if (r >= T) return 0u;
+  lf[r >> 5] = 1;
   const unsigned sh = (r & 3u) * 8u;
   const unsigned ob = (atomicAdd(tile + (r >> 2), 1u << sh) >> sh) & 0xFFu;
   return r | TC_VALID | (ob << 24);
@@ -146,17 +152,26 @@ __device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
   return false;
 }
 
-// ---- warp roles.  The last STORE_WARPS warps of the CTA do nothing but stream the zeros of
-// the CTA's BEV frames (the per-SM store path, 32 B/clk, is the longest single resource of a
-// sweep and a warp that waits on it cannot compute: tools/ubench_store.cu, ubench_zerofill.cu);
-// the other warps ("compute threads", CT of them) rasterise and meet on named barrier 1.
+// ---- warp roles.  The last warp of the CTA does nothing but write BEV images (the per-SM store
+// path, 32 B/clk, is the longest single resource of a sweep and a warp that waits on it cannot
+// compute: tools/ubench_store.cu, ubench_zerofill.cu); the other warps ("compute threads", CT of
+// them) rasterise and meet on named barrier 1.
 constexpr int STORE_WARPS = 1;
-static_assert(STORE_WARPS == 1, "the frame claim is made by lane 0 of THE zero-fill warp");
+static_assert(STORE_WARPS == 1, "one store warp: its progress word misc[4] counts whole frames");
 constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 480 compute threads
-constexpr int ST = 32 * STORE_WARPS;                   // 32 zero-fill threads
+constexpr int CW = CT / 32;                            // 15 compute warps
 constexpr int MAX_BUCKETS = 64;                        // BEV entry buckets (consecutive tiles share one beyond 64 tiles)
 constexpr int NO_BUCKET = 255;
-constexpr long long FILL_IN_IV = 320, FILL_OUT_IV = 1536;   // zero-fill pacing, cycles per 8 KB group
+constexpr long long FILL_IN_IV = 224, FILL_OUT_IV = 512;   // store-warp pacing, cycles per 8 KB group
+constexpr int ROW_CELLS = 256;                         // one output row of the store warp: 32 lanes x 32 bytes = 1 KB
+constexpr int GROUP_ROWS = 8;                          // rows per claimed group (8 KB)
+
+// ablation bits (timing experiments, tools/ablate.sh) exist only in -DSFPE_ABLATE builds
+#ifdef SFPE_ABLATE
+#define DBG(bit) ((a.debug & (bit)) != 0)
+#else
+#define DBG(bit) false
+#endif
 
 __device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(CT) : "memory"); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -167,16 +182,31 @@ __device__ __forceinline__ uint4 ld_u32x4_hint(const uint4* ptr, unsigned long l
   return v;
 }
 
+// Flags between the compute warps and the store warp live in shared memory: written with release,
+// read with acquire semantics at CTA scope (the parked bitmaps they guard are global memory, read
+// back from L2 with ld.global.cg).  No fence: a fence would also wait for every store the store
+// warp has in flight.
+__device__ __forceinline__ unsigned ld_acquire_smem(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_smem(unsigned* p, unsigned v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
 // 32-byte streaming store (STG.256, sm_100+): one L2 request per sector instead of two
 __device__ __forceinline__ void st_cs_f32x8(float* p, const float4 a, const float4 b) {
   asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w),
                "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
 }
 
+// four u8 counts -> density values; the table has an entry for every value a settled count byte
+// can hold (0..128: the saturating add never leaves a byte above 128)
 __device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
   float4 v;
-  v.x = lut[min(word & 0xFFu, 64u)]; v.y = lut[min((word >> 8) & 0xFFu, 64u)];
-  v.z = lut[min((word >> 16) & 0xFFu, 64u)]; v.w = lut[min(word >> 24, 64u)];
+  v.x = lut[word & 0xFFu]; v.y = lut[(word >> 8) & 0xFFu];
+  v.z = lut[(word >> 16) & 0xFFu]; v.w = lut[word >> 24];
   return v;
 }
 
@@ -196,13 +226,113 @@ struct FusedArgs {
   int tiles_per_bucket, n_buckets;
   long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
   unsigned* counter;   // frames claimed so far (dynamic assignment), zeroed before the launch
-  // sfpe_params.reserved[0]: ablation bits for timing experiments (tools/ablate.sh); the output is
-  // INVALID when any of 1..64, 256, 512 is set.  1 no zero fill, 2 no range stores, 4 no winner
-  // gather, 8 no resolve prefetch, 16 no BEV entry append, 32 no range atomics, 64 no point
-  // prefetch, 128 report the collision record count in `dropped`, 256 settle: loads only,
-  // 512 settle: no point loads
+  unsigned* rowbits;   // [grid][2][rows_cap / 4] parked: one byte per 1 KB output row, bit l = its 128-byte line l is non-empty
+  long long rows_cap;
+  // sfpe_params.reserved[0], -DSFPE_ABLATE builds only: ablation bits for timing experiments
+  // (tools/ablate.sh); the output is INVALID when any of 1..64, 256, 512 is set.  1 no BEV write,
+  // 2 no range stores, 4 no winner gather, 8 no resolve prefetch, 16 no BEV entry append, 32 no
+  // range atomics, 64 no point prefetch, 128 report the collision record count in `dropped`,
+  // 256 settle: loads only, 512 settle: no point loads
   int debug;
 };
+
+// ---- BEV image write-out.  Tile coordinate 0 of a frame is the 1 KB-aligned address at or below
+// its first cell, so a "row" (256 cells) is one warp-wide 32-byte store instruction covering eight
+// whole 128-byte lines.  Every line of the image is written exactly once: the lines that hold a
+// non-empty cell by the compute warps when they scan a composed tile (S2), all the others -- zeros --
+// by the store warp (and by every warp of the CTA for its last frame), which learns from the parked
+// row bitmaps which lines are whose.
+constexpr int BLOCK_ROWS = 32;                         // rows per claimed block (32 KB) = 4 groups
+constexpr int BLOCK_GROUPS = BLOCK_ROWS / GROUP_ROWS;
+struct BevJob {
+  float* bp;               // address of tile coordinate 0 (1 KB aligned; may lie before the frame)
+  const unsigned* lines;   // [n_rows / 4] one byte per row: bit l = line l of the row holds a non-empty cell (the compute warps write it)
+  int n_rows, n_blocks;
+  unsigned tbase;          // tiles this CTA had parked before the frame (misc[5] counts on from there)
+  int rpt_log2;            // rows per tile = 1 << rpt_log2
+};
+__device__ __forceinline__ BevJob make_bev_job(const FusedArgs& a, long long cells, int f, unsigned k, unsigned tbase) {
+  BevJob j;
+  float* const first = a.bev + (long long)f * cells;
+  const unsigned head = (unsigned)(((uintptr_t)first & 1023u) >> 2);
+  j.bp = first - head;
+  j.n_rows = (int)(((unsigned)cells + head + (ROW_CELLS - 1)) / ROW_CELLS);
+  j.n_blocks = (j.n_rows + BLOCK_ROWS - 1) / BLOCK_ROWS;
+  j.lines = a.rowbits + ((size_t)blockIdx.x * 2 + (k & 1u)) * (a.rows_cap >> 2);
+  j.tbase = tbase;
+  j.rpt_log2 = a.tile_log2 - 8;
+  return j;
+}
+// u8 counts of 8 cells -> density values
+__device__ __forceinline__ void lut8(const float* lut, const uint2 e, float4& v0, float4& v1) {
+  v0 = lut4(lut, e.x);
+  v1 = lut4(lut, e.y);
+}
+// A writer claims blocks of 32 rows from `cursor` (one claimer in the steady state: the store warp;
+// all warps for a CTA's last frame); the line bitmaps of the block after next are in flight while
+// the current block is written, 8 rows (8 KB) at a time.  A block is claimed once its tiles are
+// parked (misc[5]).
+// paced: one group per FILL_IN_IV cycles (25.6 B/clk) while misc[11] says that the compute warps
+// are in a phase that hardly uses the SM's path to L2 (point pass, BEV compose: registers and
+// shared memory, no waiting on loads), per FILL_OUT_IV (5.3 B/clk) while they move data
+// themselves or wait on loads, unpaced when they wait for the store warp.  (Faster inside the
+// window and every SM -- they run in step -- saturates HBM with zeros while the point loads
+// starve; measured optimum, profiles/README.md.)
+__device__ __noinline__ void bev_write_frame(const BevJob& job, unsigned* cursor, unsigned* misc, const int lane,
+                                             const bool paced) {
+  const BevJob j = job;   // in registers (the caller's copy lives in local memory)
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int myline = lane >> 2;
+  // claim the next block (-1: none left) and load its line bitmaps (lane i < 8: rows 4i..4i+3 of the
+  // block, one byte each); waits until its tiles are parked
+  auto claim = [&](int& blk, unsigned& bm) {
+    int b = 0;
+    if (lane == 0) b = (int)atomicAdd(cursor, 1u);
+    b = __shfl_sync(0xFFFFFFFFu, b, 0);
+    bm = ~0u;   // rows past the end of the frame: nothing to write
+    if (b >= j.n_blocks) { blk = -1; return; }
+    blk = b;
+    const int r_last = min((b + 1) * BLOCK_ROWS, j.n_rows) - 1;
+    const unsigned need = j.tbase + (unsigned)(r_last >> j.rpt_log2) + 1u;
+    while ((int)(ld_acquire_smem(&misc[5]) - need) < 0) __nanosleep(400);
+    const int r4 = b * BLOCK_ROWS + 4 * lane;          // first of my four rows
+    if (lane < 8 && r4 <= r_last) {
+      bm = __ldcg(j.lines + (r4 >> 2));
+      const int valid = r_last + 1 - r4;               // rows of the word that exist (1..4, or more)
+      if (valid < 4) bm |= ~0u << (8 * valid);
+    }
+  };
+  int blk, blk1, blk2;
+  unsigned bm, bm1, bm2;
+  claim(blk, bm);
+  if (blk < 0) return;
+  claim(blk1, bm1);
+  long long t_next = clock64();
+  while (blk >= 0) {
+    claim(blk2, bm2);
+#pragma unroll
+    for (int s = 0; s < BLOCK_GROUPS; ++s) {
+      float* const p = j.bp + ((size_t)blk * BLOCK_ROWS + s * GROUP_ROWS) * ROW_CELLS + lane * 8;
+#pragma unroll
+      for (int u = 0; u < GROUP_ROWS; ++u) {
+        const int row = s * GROUP_ROWS + u;            // row of the block
+        const unsigned w = __shfl_sync(0xFFFFFFFFu, bm, row >> 2);
+        if (((w >> ((row & 3) * 8 + myline)) & 1u) == 0u) st_cs_f32x8(p + u * ROW_CELLS, z, z);
+      }
+      if (paced) {
+        for (;;) {
+          const unsigned wdw = *reinterpret_cast<volatile unsigned*>(&misc[11]);
+          const long long rem = t_next + (wdw == 2u ? 0ll : wdw == 1u ? FILL_IN_IV : FILL_OUT_IV) - clock64();
+          if (rem <= 0) break;
+          __nanosleep((unsigned)min(rem >> 1, 2000ll) + 20u);
+        }
+        t_next = clock64();
+      }
+    }
+    blk = blk1; bm = bm1;
+    blk1 = blk2; bm1 = bm2;
+  }
+}
 
 // phase stamps: thread 0 adds the cycles since the previous stamp to slot `ph` (accumulated in
 // shared memory, written out once at the end of the kernel)
@@ -222,83 +352,40 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   unsigned* const tile = smem;   // S2      : packed u8 BEV counts
   float* const lut = reinterpret_cast<float*>(smem + main_words);
   // misc: [0] deferred count, [1] status bits, [2] dropped, [3] tile redo flag,
-  //       [4] zero-fill progress: += 1 per store warp per finished frame, [5] frames begun by the compute warps,
-  //       [6] last frame period of the compute warps in SM cycles, [7] collision records
-  unsigned* const misc = smem + main_words + 72;
+  //       [4] frames whose BEV image the store warp has written, [5] tiles parked so far (all frames),
+  //       [6] frames claimed so far, [7] collision records, [9] claim broadcast, [10] parked sectors of the
+  //       frame in S2, [11] store-warp pacing window, [12..15] claim ring: frame + 1 (~0: no more frames),
+  //       [16..31] phase cycles, [32..95] entries per bucket, [96..99] ring: misc[5] when the frame was
+  //       claimed, [100..101] group cursor of the frame being written (by frame parity)
+  unsigned* const misc = smem + main_words + 136;
   const int tid = threadIdx.x;
   const int hw = g.H * g.W;
   const long long cells = (long long)g.nbx * g.nby;
   const bool do_bev = g.enable_bev && a.bev;
   const int f_end = a.fs.frame0 + a.fs.n_frames;
-  // zero-fill warps active?  (debug bit 0 and BEV off need none)
-  const bool self_claim = !do_bev || (a.debug & 1);
-  if (tid < 65) lut[tid] = (float)a.lut64[tid];
+  const bool store_active = do_bev && !DBG(1);   // is there a BEV image to write?
+  if (tid < 129) lut[tid] = (float)a.lut64[min(tid, 64)];
   if (tid < 16) misc[tid] = 0u;
+  if (tid >= 96 && tid < 104) misc[tid] = 0u;
   long long* const prof_acc = reinterpret_cast<long long*>(misc + 16);   // [8], thread 0 only
   if (tid == 0)
     for (int k = 0; k < 8; ++k) prof_acc[k] = 0;
   __syncthreads();   // the only CTA-wide barrier: the roles part here
 
-  // ======================================================================== zero-fill warps
+  // ======================================================================== store warp
   if (tid >= CT) {
-    if (self_claim) { if ((tid & 31) == 0) atomicAdd(&misc[4], 0x10000000u); return; }   // no fill: the compute warps claim frames themselves
-    const int st = tid - CT;
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!store_active) return;
+    const int sl = tid - CT;
     for (unsigned k = 0;; ++k) {
-      // at most one frame ahead of the compute warps: the fill of frame k runs next to the
-      // rasterisation of frame k-1 (an unbounded run-ahead would saturate HBM with zeros first
-      // and starve the point pass of every SM)
-      while (*reinterpret_cast<volatile unsigned*>(&misc[5]) < k) __nanosleep(2000);
-      // frames are claimed dynamically (CTAs start staggered and drift); the claim is handed
-      // to the compute warps through misc[12 + (k & 3)] = frame + 1 (~0 = no more frames)
-      int f = 0;
-      if (st == 0) {
-        f = a.fs.frame0 + (int)atomicAdd(a.counter, 1u);
-        *reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]) = f < f_end ? (unsigned)f + 1u : ~0u;
-      }
-      f = __shfl_sync(0xFFFFFFFFu, f, 0);
-      if (f >= f_end) return;
-      // this frame's BEV is cells [E0, E1) of a.bev: full 16-byte words [W0, W1) + head / tail cells
-      const long long E0 = (long long)f * cells, E1 = E0 + cells;
-      const long long W0 = (E0 + 3) >> 2, W1 = E1 >> 2;
-      if (st < 8) {   // head cells [E0, 4*W0) and tail cells [4*W1, E1), clipped to the frame
-        const long long c = st < 4 ? E0 + st : 4 * W1 + (st - 4);
-        const bool mine = st < 4 ? (c < 4 * W0 && c < E1) : (c >= E0 && c < E1);
-        if (mine) a.bev[c] = 0.f;
-      }
-      // 32-byte stores: [W0, W1) in 16-byte words = an optional leading word to reach 32-byte
-      // alignment, then pairs, then an optional trailing word
-      long long V0 = W0, V1 = W1;
-      if ((V0 & 1) && V0 < V1) { if (st == 8) reinterpret_cast<float4*>(a.bev)[V0] = z; ++V0; }
-      if (((V1 - V0) & 1) && V0 < V1) { if (st == 9) reinterpret_cast<float4*>(a.bev)[V1 - 1] = z; --V1; }
-      float* p = a.bev + 4 * V0 + 8 * (long long)st;
-      long long left = ((V1 - V0) >> 1) - st;   // 32-byte units from p to the end of the frame
-      // Paced at two rates, one group of 8 x 32 lanes x 32 bytes (8 KB) at a time.  The SM's
-      // path to L2 carries 32 B/clk and every phase of the compute warps that moves data itself
-      // (range resolve, BEV sector write-out) slows down by what the fill takes from it, while
-      // the point pass and the BEV compose hardly use it (and do not wait on loads): the
-      // fill runs at FILL_IN_IV cycles per group (25.6 B/clk) while misc[11] says such a phase
-      // is running, at FILL_OUT_IV (5.3 B/clk) otherwise, and unpaced when the compute warps
-      // wait for it.  (Faster inside the window and every SM -- they run in step -- saturates
-      // HBM with zeros while the point loads starve; measured optimum, profiles/README.md.)
-      long long t_next = clock64();
-      for (; left > 7 * ST; left -= 8 * ST, p += 8 * 8 * ST) {
-#pragma unroll
-        for (int u = 0; u < 8; ++u) st_cs_f32x8(p + u * 8 * ST, z, z);
-        for (;;) {
-          const unsigned wdw = *reinterpret_cast<volatile unsigned*>(&misc[11]);
-          const long long rem = t_next + (wdw == 2u ? 0ll : wdw == 1u ? FILL_IN_IV : FILL_OUT_IV) - clock64();
-          if (rem <= 0) break;
-          __nanosleep((unsigned)min(rem >> 1, 2000ll) + 20u);
-        }
-        t_next = clock64();
-      }
-      for (; left > 0; left -= ST, p += 8 * ST) st_cs_f32x8(p, z, z);
-      __threadfence_block();
+      // frame k of this CTA: claimed by the compute warps (ring), written as its tiles get parked
+      while ((int)(ld_acquire_smem(&misc[6]) - (k + 1u)) < 0) __nanosleep(1000);
+      const unsigned c = *reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]);
+      if (c == ~0u) return;
+      const BevJob j = make_bev_job(a, cells, (int)c - 1, k, *reinterpret_cast<volatile unsigned*>(&misc[96 + (k & 3u)]));
+      bev_write_frame(j, &misc[100 + (k & 1u)], misc, sl, true);
       __syncwarp();
-      if ((tid & 31) == 0) atomicAdd(&misc[4], 1u);
+      if (sl == 0) st_release_smem(&misc[4], k + 1u);   // the parked bitmaps of frame k may be overwritten
     }
-    return;
   }
 
   // ======================================================================== compute warps
@@ -315,20 +402,19 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const int bucket_shift = a.tile_log2 + 31 - __clz(a.tiles_per_bucket);   // tiles_per_bucket is a power of two
   long long t_prev = clock64();
   unsigned frames_done = 0;
-  long long t_frame = 0;
 
   for (;; ++frames_done) {
     if (tid == 0) {
-      unsigned c;
-      if (self_claim) {
-        const int fc = a.fs.frame0 + (int)atomicAdd(a.counter, 1u);
-        c = fc < f_end ? (unsigned)fc + 1u : ~0u;
-      } else {
-        volatile unsigned* slot = &misc[12 + (frames_done & 3u)];
-        while ((c = *slot) == 0u) __nanosleep(100);
-        *slot = 0u;
-      }
+      // frames are claimed dynamically (CTAs start staggered and drift); the store warp learns the
+      // claim through the ring misc[12 + (k & 3)] (it is never more than two frames behind)
+      const int fc = a.fs.frame0 + (int)atomicAdd(a.counter, 1u);
+      const unsigned c = fc < f_end ? (unsigned)fc + 1u : ~0u;
       misc[9] = c;
+      if (store_active) {
+        *reinterpret_cast<volatile unsigned*>(&misc[12 + (frames_done & 3u)]) = c;
+        *reinterpret_cast<volatile unsigned*>(&misc[96 + (frames_done & 3u)]) = misc[5];
+        st_release_smem(&misc[6], frames_done + 1u);
+      }
     }
     compute_sync();
     const unsigned claimed = misc[9];
@@ -338,21 +424,20 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     long long base, n;
     frame_span(a.fs, f, base, n);
     const float4* __restrict__ fp = a.pts + base;
-    const long long E0 = (long long)f * cells, E1 = E0 + cells;
-    const unsigned head = (unsigned)(E0 & 7);   // tiles start on a 32-byte sector of the output
+    // tile coordinate 0 of the frame's BEV = the 1 KB-aligned address at or below its first cell
+    const unsigned head = do_bev ? (unsigned)(((uintptr_t)(a.bev + (long long)f * cells) & 1023u) >> 2) : 0u;
 
     // ---- S0
-    if (g.enable_range)
-      for (int i = tid; i < hw; i += CT) keys[i] = KEY32_EMPTY;
+    if (g.enable_range) {   // 16-byte stores (smem is 16-byte aligned, the tail word by word)
+      const uint4 e4 = make_uint4(KEY32_EMPTY, KEY32_EMPTY, KEY32_EMPTY, KEY32_EMPTY);
+      for (int i = tid; i < (hw >> 2); i += CT) reinterpret_cast<uint4*>(keys)[i] = e4;
+      if (tid < (hw & 3)) keys[(hw & ~3) + tid] = KEY32_EMPTY;
+    }
     if (tid < 4) misc[tid] = 0u;
     if (tid >= 32 && tid < 32 + MAX_BUCKETS) misc[tid] = 0u;
     if (tid == 0) {
       misc[7] = 0u; misc[8] = 0u; misc[9] = 0u;
-      misc[5] = frames_done + 1;   // lets the zero-fill warps start on the next frame
-      misc[11] = 1u;               // fill window open (see the zero-fill warps)
-      const long long now = clock64();
-      if (frames_done) misc[6] = (unsigned)min(now - t_frame, 0x7FFFFFFFll);   // frame period for the fill pacing
-      t_frame = now;
+      misc[11] = 1u;               // the point pass hardly uses the path to L2: store-warp window open
     }
     // the first two S1 iterations of points are pulled into L2 while the keys are initialised
     for (long long l = tid; l * 8 < n && l < 3 * (4 * CT / 8); l += CT) prefetch_l2(fp + l * 8);
@@ -373,7 +458,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     auto rasterise4 = [&](const float4 (&v)[4], const int i0) {
       {  // L2 prefetch three iterations ahead (one 128-byte line = 8 points per thread)
         const int l = i0 + 3 * 4 * CT + tid * 8;
-        if (tid < 4 * CT / 8 && l < n32 && !(a.debug & 64)) prefetch_l2(fp + l);
+        if (tid < 4 * CT / 8 && l < n32 && !DBG(64)) prefetch_l2(fp + l);
       }
       // Per point, branch-free (so that the four points of a thread interleave): every decision
       // -- range-scan cell, range bucket, BEV bins -- is made in fp32 and PROVEN by its guard
@@ -435,7 +520,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         if (defer[u]) my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)(i0 + u * CT + tid);
       // BEV entries are appended to the bucket of their tile, one shared-memory atomic per
       // (warp, bucket): lanes with the same bucket elect a leader that reserves the slots
-      if (do_bev && !(a.debug & 16)) {
+      if (do_bev && !DBG(16)) {
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const unsigned m = __match_any_sync(0xFFFFFFFFu, bb[u]);
@@ -449,7 +534,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       // the four shared-memory atomics go out back to back; their results are looked at afterwards
       unsigned old[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !(a.debug & 32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
+      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !DBG(32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
 #pragma unroll
       for (int u = 0; u < 4; ++u) note_collision(my_cq, misc, cell[u], key[u], old[u]);
     };
@@ -522,11 +607,11 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             if (!act[u]) continue;
             cur[u] = keys[en[u].x];
             if ((cur[u] & IDX_MASK32) == en[u].y) { act[u] = false; continue; }   // the holder itself has nothing to do
-            if (a.debug & 512) { pv[u] = make_float4(1.f, 2.f, 3.f, (float)en[u].y); hv[u] = make_float4(1.f, 2.f, 3.f, (float)cur[u]); continue; }
+            if (DBG(512)) { pv[u] = make_float4(1.f, 2.f, 3.f, (float)en[u].y); hv[u] = make_float4(1.f, 2.f, 3.f, (float)cur[u]); continue; }
             pv[u] = __ldg(fp + en[u].y);
             hv[u] = __ldg(fp + (cur[u] & IDX_MASK32));
           }
-          if (a.debug & 256) {
+          if (DBG(256)) {
 #pragma unroll
             for (int u = 0; u < 4; ++u)
               if (act[u] && pv[u].x + hv[u].y == 1.2345f) keys[0] = 0u;
@@ -541,7 +626,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       PROF_STAMP(7);
       if (tid == 0) {
         if (a.status) a.status[f] = (int)misc[1];
-        if (a.dropped) a.dropped[f] = (a.debug & 128) ? (int)misc[7] : (int)misc[2];
+        if (a.dropped) a.dropped[f] = DBG(128) ? (int)misc[7] : (int)misc[2];
       }
 
       // ---- S1c: resolve the range scan; output row r shows pre-flip row H-1-r   (:74)
@@ -585,7 +670,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             if (++col == g.W) { col = 0; ++orow; }
           }
         };
-        if (!(a.debug & 8)) {
+        if (!DBG(8)) {
 #pragma unroll 1
           for (int s = 1; s < PF; ++s) {   // prologue of the prefetch stream
             int r;
@@ -615,7 +700,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           float4 v[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) { key[j] = nkey[j]; v[j] = nv[j]; }
-          if (!(a.debug & 8)) {
+          if (!DBG(8)) {
             int pr;
             const int pc = task_cell(t + PF * CT, pr);
             if (pc >= 0) {
@@ -631,7 +716,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             load_keys(nc, nr, nkey);
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-              if (nkey[j] != KEY32_EMPTY) nv[j] = (a.debug & 4) ? make_float4(1.f, 2.f, 3.f, (float)nkey[j]) : __ldg(fp + (nkey[j] & IDX_MASK32));
+              if (nkey[j] != KEY32_EMPTY) nv[j] = DBG(4) ? make_float4(1.f, 2.f, 3.f, (float)nkey[j]) : __ldg(fp + (nkey[j] & IDX_MASK32));
           }
           if (c < 0) continue;
           float d[4], h[4], it[4];
@@ -646,7 +731,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
               h[j] = v[j].z; it[j] = v[j].w;
             }
           }
-          if (a.debug & 2) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
+          if (DBG(2)) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
           if (a.range) {
             if (a.range_layout == 0) {
               float* o = a.range + (size_t)f * 3 * hw + c;
@@ -702,15 +787,33 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       if (a.dropped) a.dropped[f] = 0;
     }
 
-    // ---- S2: BEV, one flat tile of the output at a time.  Tiles are T = 2^tile_log2 cells and
-    // start on a 32-byte sector of the output (tile coordinates = frame cell + head).  Shared
-    // memory now holds the u8 counts of the tile, nothing else: the non-empty 32-byte sectors are
-    // found by scanning the tile (one 8-byte shared load per sector, most of them zero).
+    // ---- S2: BEV, one flat tile of the output at a time.  Tiles are T = 2^tile_log2 cells of
+    // tile coordinates (= frame cell + head; coordinate 0 is 1 KB aligned in the output).  Shared
+    // memory now holds the u8 counts of the tile, nothing else.  A composed tile is scanned one
+    // output row (32 sectors of 8 cells = 8 lines of 128 bytes) per warp step: the lines with a
+    // non-empty cell are converted and written here, whole, and the row's bitmap is parked for the
+    // store warp, which writes all the other lines (zeros).
     if (do_bev) {
       const int T = 1 << a.tile_log2, tw = T >> 2;
-      for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+      const unsigned par = frames_done & 1u;
+      unsigned* const bm_k = a.rowbits + ((size_t)blockIdx.x * 2 + par) * (a.rows_cap >> 2);   // one byte per row
+      unsigned char* const lf = reinterpret_cast<unsigned char*>(tile + tw);   // line flags of the tile: byte (cell >> 5)
+      const int lbw = T >> 7;                  // words of the line flags (8 bytes per row)
+      if (tid == 0) {
+        misc[11] = 1u;   // compose works in shared memory: store-warp window open
+        // the parking area of this frame parity is free once the store warp has written frame k-2
+        if (store_active && frames_done >= 2u && (int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) {
+          misc[11] = 2u;   // we wait for the store warp: unpaced
+          while ((int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) __nanosleep(200);
+          misc[11] = 1u;
+        }
+        misc[100 + par] = 0u;
+      }
+#ifdef SFPE_PROFX
+      PROF_STAMP(0);
+#endif
+      for (int w = tid; w < ((tw + lbw) >> 2); w += CT) reinterpret_cast<uint4*>(tile)[w] = make_uint4(0u, 0u, 0u, 0u);   // tw, lbw: multiples of 4
       compute_sync();
-      const long long B0 = E0 - head;          // global cell of tile coordinate 0
       const unsigned span_all = (unsigned)cells + head;
       const int n_tiles = (int)((span_all + (unsigned)T - 1u) >> a.tile_log2);
       // entries of a tile's bucket, ENTRY_BATCH 16-byte loads per thread; slots past the end of
@@ -732,7 +835,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           }
         }
       };
-      uint4 pe[ENTRY_BATCH];   // first batch of the next tile, loaded while the current tile is written out
+      uint4 pe[ENTRY_BATCH];   // first batch of the next tile, loaded while the current tile is scanned
       load_batch(0, 0u, pe);
       for (int t = 0; t < n_tiles; ++t) {
         const unsigned tlo = (unsigned)t << a.tile_log2;                 // tile coordinates of this tile
@@ -740,7 +843,6 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         const unsigned cnt = bcnt[bkt];
         const unsigned n4 = (cnt + 3u) >> 2;
         bool danger = false;
-        if (tid == 0) misc[11] = 1u;   // compose works in shared memory: fill window open
         if (n4 == 0u && t + 1 < n_tiles) load_batch(t + 1, 0u, pe);
         for (unsigned q0 = 0; q0 < n4; q0 += ENTRY_BATCH * CT) {
           uint4 e[ENTRY_BATCH];
@@ -752,10 +854,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           // stage 1: all counts go out back to back; every slot keeps (position | valid | old byte << 24)
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            e[u].x = tile_count_issue(tile, e[u].x - tlo, (unsigned)T);
-            e[u].y = tile_count_issue(tile, e[u].y - tlo, (unsigned)T);
-            e[u].z = tile_count_issue(tile, e[u].z - tlo, (unsigned)T);
-            e[u].w = tile_count_issue(tile, e[u].w - tlo, (unsigned)T);
+            e[u].x = tile_count_issue(tile, lf, e[u].x - tlo, (unsigned)T);
+            e[u].y = tile_count_issue(tile, lf, e[u].y - tlo, (unsigned)T);
+            e[u].z = tile_count_issue(tile, lf, e[u].z - tlo, (unsigned)T);
+            e[u].w = tile_count_issue(tile, lf, e[u].w - tlo, (unsigned)T);
           }
           // stage 2: saturation fix-ups (rare)
 #pragma unroll
@@ -767,78 +869,117 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           }
         }
         if (danger) misc[3] = 1u;
-        // the zeros of this frame must have been issued before its non-empty sectors go out
-        if (tid == 0) {
-          const unsigned want = (unsigned)STORE_WARPS * (frames_done + 1);
-          if (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) {
-            misc[11] = 2u;   // we wait for the fill: window open
-            while (*reinterpret_cast<volatile unsigned*>(&misc[4]) < want) __nanosleep(200);
-          }
-          misc[11] = 0u;     // the sector write-out stores to global memory: window closed
-          __threadfence_block();
-        }
         compute_sync();
         PROF_STAMP(4);
         if (misc[3]) {  // a byte may have wrapped: redo this tile with the exact (CAS) form
           compute_sync();
           if (tid == 0) misc[3] = 0u;
-          for (int w = tid; w < tw; w += CT) tile[w] = 0u;
+          for (int w = tid; w < tw + lbw; w += CT) tile[w] = 0u;
           compute_sync();
           const unsigned* const bucket = my_buckets + (size_t)bkt * a.per_cta;
           for (unsigned i = tid; i < cnt; i += CT) {
             const unsigned r = __ldcg(bucket + i) - tlo;
-            if (r < (unsigned)T) tile_count_exact(tile, r);
+            if (r < (unsigned)T) { tile_count_exact(tile, r); lf[r >> 5] = 1; }
           }
           compute_sync();
           PROF_STAMP(5);
         }
-        // write the non-empty sectors (8 cells = 32 bytes) over the zero fill; re-zero what was used
+        // write-out.  (1) Warp w takes rows [w*chunk, (w+1)*chunk) of the tile, a lane two rows (16 line
+        // flags -> 16 bits): the bits are parked for the store warp (which writes every line NOT
+        // marked) and expanded into the tile's list of lines (one shared-memory atomic per warp).
+        // (2) All warps share the list, eight lines per warp step: the four lanes of a line take one
+        // 32-byte sector each (LUT of the counts, zeros included) and write it -- one full-line
+        // request per non-empty line -- and re-zero the tile.  The first and the last row of the
+        // frame share their lines with the neighbouring frames: all their lines are marked here and
+        // written cell by cell.
         {
-          const long long B = B0 + tlo;                          // global cell of the tile's first cell
-          const int rel_lo = t == 0 ? (int)head : 0;             // cells of THIS frame inside the tile
-          const long long rem = (long long)span_all - tlo;
-          const int rel_hi = rem < T ? (int)rem : T;
+          const int rpt = T >> 8;                   // rows per tile
+          const int chunk = ((rpt + CW - 1) / CW + 3) & ~3;   // <= 64 (T <= 2^17)
+          const int rlo = (tid >> 5) * chunk, rhi = min(rlo + chunk, rpt);
+          const int n_rows = (int)((span_all + (ROW_CELLS - 1)) / ROW_CELLS);
           uint2* const tile2 = reinterpret_cast<uint2*>(tile);
-          float4* const o4 = reinterpret_cast<float4*>(a.bev + B);
-          const int n_sct = (rel_hi + 7) >> 3;
-          // Two steps per warp, no CTA barrier in between: (1) scan the warp's sectors, 32 at a
-          // time, and list the non-empty ones (shared memory behind the tile; ~15 % of them);
-          // (2) all lanes convert and write one listed sector each.  The scan steps are light and
-          // independent, the conversion runs with full warps.
-          const int wcap = (((T >> 3) + CT - 1) / CT) * 32;
-          unsigned* const wlist = tile + (T >> 2) + (tid >> 5) * wcap;
-          unsigned wn = 0u;   // warp-uniform
-#pragma unroll 4
-          for (int base = (tid >> 5) << 5; base < n_sct; base += CT) {
-            const int sct = base + lane;
-            uint2 w = make_uint2(0u, 0u);
-            if (sct < n_sct) w = tile2[sct];
-            const bool nz = (w.x | w.y) != 0u;
-            const unsigned m = __ballot_sync(0xFFFFFFFFu, nz);
-            if (nz) wlist[wn + (unsigned)__popc(m & lane_lt)] = (unsigned)sct;
-            wn += (unsigned)__popc(m);
-          }
-          __syncwarp();
-          for (unsigned j = lane; j < wn; j += 32u) {
-            const int sct = (int)wlist[j];
-            const uint2 w = tile2[sct];
-            tile2[sct] = make_uint2(0u, 0u);
-            const float4 v0 = lut4(lut, w.x), v1 = lut4(lut, w.y);
-            const int c0 = sct << 3;
-            if (c0 >= rel_lo && c0 + 8 <= rel_hi) {
-              st_cs_f32x8(reinterpret_cast<float*>(o4 + 2 * sct), v0, v1);
-            } else {  // frame head / tail: only the cells of THIS frame
-              const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+          unsigned short* const wl = reinterpret_cast<unsigned short*>(tile + tw + lbw);   // [T / 32] lines of the tile
+          {
+            const int r = rlo + 2 * lane;           // my two rows: r, r + 1 (rlo, rhi are multiples of 4 or the tile's end)
+            unsigned b16 = 0u;
+            if (r < rhi) {
+              const uint4 v = reinterpret_cast<uint4*>(lf)[r >> 1];
+              if ((v.x | v.y | v.z | v.w) != 0u) reinterpret_cast<uint4*>(lf)[r >> 1] = make_uint4(0u, 0u, 0u, 0u);
+              b16 = ((v.x * 0x01020408u) >> 24) | (((v.y * 0x01020408u) >> 24) << 4) |
+                    (((v.z * 0x01020408u) >> 24) << 8) | (((v.w * 0x01020408u) >> 24) << 12);
+              const int row = t * rpt + r;
+              if (row == 0 || row == n_rows - 1) b16 |= 0x00FFu;
+              if (row + 1 == n_rows - 1) b16 |= 0xFF00u;
+            }
+            // parked: four rows per word
+            const unsigned hi = __shfl_down_sync(0xFFFFFFFFu, b16, 1);
+            if ((lane & 1) == 0 && r < rhi) bm_k[((size_t)t * rpt + r) >> 2] = b16 | (hi << 16);
+            const unsigned cnt = (unsigned)__popc(b16);
+            unsigned inc = cnt;                     // inclusive prefix of the line counts over the lanes
 #pragma unroll
-              for (int k = 0; k < 8; ++k)
-                if (c0 + k >= rel_lo && c0 + k < rel_hi && vv[k] != 0.f) a.bev[B + c0 + k] = vv[k];
+            for (int d = 1; d < 32; d <<= 1) {
+              const unsigned o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+              if (lane >= d) inc += o;
+            }
+            const unsigned wtot = __shfl_sync(0xFFFFFFFFu, inc, 31);
+            unsigned off = 0u;
+            if (lane == 0 && wtot) off = atomicAdd(&misc[10], wtot);
+            off = __shfl_sync(0xFFFFFFFFu, off, 0) + inc - cnt;
+            const unsigned base = (unsigned)r << 3; // line index (within the tile) of bit 0
+            while (b16) {
+              const unsigned b = (unsigned)__ffs(b16) - 1u;
+              b16 &= b16 - 1u;
+              wl[off++] = (unsigned short)(base + b);
+            }
+          }
+          compute_sync();
+#ifdef SFPE_PROFX
+          PROF_STAMP(2);
+#endif
+          if (tid == 0) misc[11] = 0u;   // the write-out stores to global memory: store-warp window closed
+          const unsigned wn = misc[10];
+          float* const bp = a.bev + (long long)f * cells - head;   // tile coordinate 0
+          for (unsigned j = (unsigned)(tid >> 2); j < wn; j += CT / 4) {
+            const unsigned li = wl[j];
+            const int r = (int)(li >> 3), sct = (int)((li & 7u) << 2) + (lane & 3);
+            const uint2 w = tile2[r * 32 + sct];
+            tile2[r * 32 + sct] = make_uint2(0u, 0u);
+            float4 v0, v1;
+            lut8(lut, w, v0, v1);
+            const int row = t * rpt + r;
+            float* const o = bp + (size_t)row * ROW_CELLS + sct * 8;
+            if (row > 0 && row < n_rows - 1) {
+              st_cs_f32x8(o, v0, v1);
+            } else {
+              const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+              const unsigned c0 = (unsigned)row * ROW_CELLS + (unsigned)sct * 8u;
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                if (c0 + q >= head && c0 + q < span_all) o[q] = vv[q];
             }
           }
         }
         compute_sync();
+        if (tid == 0) {   // the tile's bitmaps are parked: the store warp may write its rows
+          st_release_smem(&misc[5], misc[5] + 1u);
+          misc[11] = 1u;
+          misc[10] = 0u;   // the next tile's list
+        }
         PROF_STAMP(6);
       }
     }
+  }
+  // The compute warps are done; the store warp is up to two frames behind.  All warps now write what
+  // is left of the CTA's last two frames (the store warp joins in as it gets there: every block is
+  // claimed from the frame's cursor exactly once).
+  if (store_active && frames_done > 0u) {
+    if (tid == 0) misc[11] = 2u;
+    for (unsigned k = frames_done >= 2u ? frames_done - 2u : 0u; k < frames_done; ++k) {
+      const int fk = (int)*reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]) - 1;
+      const BevJob j = make_bev_job(a, cells, fk, k, *reinterpret_cast<volatile unsigned*>(&misc[96 + (k & 3u)]));
+      bev_write_frame(j, &misc[100 + (k & 1u)], misc, lane, false);
+    }
+    PROF_STAMP(5);
   }
   if (a.prof && tid == 0)
     for (int k = 0; k < 8; ++k) a.prof[(size_t)blockIdx.x * 8 + k] += prof_acc[k];
@@ -852,15 +993,20 @@ static int main_words_max() { return SMEM_LIMIT / 4 - SMEM_MISC_WORDS; }
 // bytes of shared memory; at most MAX_BUCKETS entry buckets, consecutive tiles share a bucket.
 FusedGeom fused_geometry(const DevGrid& g) {
   FusedGeom o;
-  o.tile_log2 = 6; o.tiles_per_bucket = 1; o.n_buckets = 1; o.s2_words = 0;
+  o.tile_log2 = 10; o.tiles_per_bucket = 1; o.n_buckets = 1; o.s2_words = 0; o.rows_cap = 1;
   if (!g.enable_bev) return o;
   const long long cells = (long long)g.nbx * g.nby;
-  auto words = [](int p) { const long long T = 1ll << p; return (int)(T / 4 + (CT / 32) * (((T >> 3) + CT - 1) / CT) * 32); };
-  int p = 6;
-  while (p < 22 && (1ll << p) < cells + 8 && words(p + 1) <= main_words_max()) ++p;
+  // tile counts + line flags (a byte per 32 cells) + per-warp lists of non-empty lines (u16 each, 8 per row of the warp's share)
+  auto words = [](int p) {
+    const long long T = 1ll << p;
+    return (int)(T / 4 + (T >> 7) + (T >> 6));
+  };
+  int p = 10;   // a tile is at least four output rows (1024 cells = one word of the line bitmap)
+  while (p < 22 && (1ll << p) < cells + ROW_CELLS && words(p + 1) <= main_words_max()) ++p;
   o.tile_log2 = p;
   o.s2_words = (words(p) + 3) & ~3;
-  const long long n_tiles = (cells + 7 + (1ll << p) - 1) >> p;
+  const long long n_tiles = (cells + (ROW_CELLS - 1) + (1ll << p) - 1) >> p;   // head <= 255
+  o.rows_cap = n_tiles << (p - 8);
   o.tiles_per_bucket = 1;   // a power of two: the bucket of an entry is a shift
   while ((n_tiles + o.tiles_per_bucket - 1) / o.tiles_per_bucket > MAX_BUCKETS) o.tiles_per_bucket *= 2;
   o.n_buckets = (int)((n_tiles + o.tiles_per_bucket - 1) / o.tiles_per_bucket);
@@ -872,8 +1018,8 @@ bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, l
                       src.oi == 12 && ((uintptr_t)src.data & 15) == 0;
   if (!packed || g.use_extrinsic || g.n_slices || max_n > FUSED_MAX_N) return false;
   if (g.enable_range && (out.range_dtype != 0 || g.H * g.W > main_words_max())) return false;
-  if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts || ((uintptr_t)out.bev & 31) != 0)) return false;   // 32-byte stores
-  if (g.enable_bev && (long long)g.nbx * g.nby > 0x7FFFFFF0ll) return false;
+  if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts)) return false;
+  if (g.enable_bev && (long long)g.nbx * g.nby > 0x7FFFFF00ll) return false;
   return g.enable_range || g.enable_bev;
 }
 
@@ -883,17 +1029,15 @@ int fused_grid(int device, int n_frames) {
   return n_frames < sms ? n_frames : sms;
 }
 
+cudaError_t prepare_fused() {
+  // per device (per primary context): called from sfpe_create after cudaSetDevice
+  return cudaFuncSetAttribute(k_fused_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+}
+
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
                          const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_fused_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
-  }
-  const long long cells = (long long)g.nbx * g.nby;
   int s2_words = 0;
-  FusedGeom geo = fused_geometry(g);
+  const FusedGeom geo = fused_geometry(g);
   if (g.enable_bev) s2_words = geo.s2_words;
   int main_words = g.enable_range ? g.H * g.W : 0;
   if (s2_words > main_words) main_words = s2_words;
@@ -902,6 +1046,7 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.pts = reinterpret_cast<const float4*>(src.data);
   a.fs = fs;
   a.entries = fx.entries; a.queue = fx.queue; a.cqueue = reinterpret_cast<uint2*>(fx.cqueue); a.per_cta = fx.per_cta;
+  a.rowbits = fx.rowbits; a.rows_cap = geo.rows_cap;
   a.lut64 = s.lut;
   a.counter = fx.counter;
   { cudaError_t e = cudaMemsetAsync(fx.counter, 0, sizeof(unsigned), st); if (e != cudaSuccess) return e; }

@@ -81,15 +81,17 @@ struct FusedScratch {
   unsigned* queue;     // [grid][per_cta]
   unsigned* cqueue;    // [grid][12*per_cta] words: collision records
   unsigned* counter;   // frame claim counter (zeroed by launch_fused)
+  unsigned* rowbits;   // [grid][2][rows_cap]: parked BEV row bitmaps (non-empty sectors)
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
   long long* prof;     // optional [grid][8] phase cycle accumulators
-  int debug;           // sfpe_params.reserved[0]: bit 0 = skip the BEV zero fill (timing experiments only)
+  int debug;           // sfpe_params.reserved[0]: ablation bits (-DSFPE_ABLATE builds only)
 };
-struct FusedGeom { int tile_log2, tiles_per_bucket, n_buckets, s2_words; };
+struct FusedGeom { int tile_log2, tiles_per_bucket, n_buckets, s2_words; long long rows_cap; };
 FusedGeom fused_geometry(const DevGrid& g);
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n);
 int fused_grid(int device, int n_frames);
+cudaError_t prepare_fused();   // per device: opt in to the large dynamic shared memory size
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
                          const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches);
 

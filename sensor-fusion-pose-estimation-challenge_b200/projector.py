@@ -81,7 +81,7 @@ class LidarProjector:
     def last_path(self):
         return self.lib.sfpe_last_path(self._ctx).decode()
 
-    PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo", "bev_write", "settle")
+    PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo_and_tail_write", "bev_park", "settle")
 
     def phase_profile(self, enable=True):
         """Switch the fused kernel's per-phase SM-cycle counters on (and reset them) or off."""

@@ -113,7 +113,7 @@ def test_back_project_matches_reference_golden():
     assert moved.sum() >= 4 and zeroed.sum() >= 2 and (~moved).sum() >= 3     # the fixture exercises every branch
 
 
-@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+@pytest.mark.skipif(not rl.full_tree_available(), reason="reference tree not mounted")
 def test_back_project_equals_live_reference(synth):
     dist, hgt, cen, box = synth.make_back_project_case(n_items=18, seed=7)
     c1, b1, c2, b2 = cen.copy(), box.copy(), cen.copy(), box.copy()
@@ -152,7 +152,7 @@ def test_find_bbox_3d_matches_reference_golden(synth):
         assert len(lo.decode_boxes(dist.astype(np.float64), hgt.astype(np.float64), y, bb, c3)) > 100
 
 
-@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+@pytest.mark.skipif(not rl.full_tree_available(), reason="reference tree not mounted")
 def test_find_bbox_3d_equals_live_reference(synth):
     for seed, strays in ((11, 0), (12, 12)):
         dist, hgt, y, bb, c3 = synth.make_bbox_decode_case(seed=seed, strays=strays)
@@ -179,14 +179,14 @@ def test_find_obstacle_matches_reference_golden(synth):
         assert [int(v) for v in got] == [int(v) for v in row[1:]]
 
 
-@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+@pytest.mark.skipif(not rl.full_tree_available(), reason="reference tree not mounted")
 def test_find_obstacle_equals_live_reference(synth):
     for seed in (40, 41, 42):
         y = synth.make_obstacle_case(seed=seed, blobs=7, speckle=0.01)
         assert _obstacle_tuple(rl.find_obstacle_fn()(y, (32, 1801, 3))) == _obstacle_tuple(lo.find_obstacle(y, (32, 1801, 3)))
 
 
-@pytest.mark.skipif(not rl.available(), reason="reference tree not mounted")
+@pytest.mark.skipif(not rl.full_tree_available(), reason="reference tree not mounted")
 def test_post_network_chain_equals_live_reference(synth):
     """find_obstacle -> back_project_2D_2_3D -> find_bbox_3d as predict_point_cloud chains them (:347-362)."""
     fns = (rl.find_obstacle_fn(), rl.back_project_fn(), rl.find_bbox_3d_fn())
