@@ -250,7 +250,8 @@ def run_ours(a):
     host_all = np.concatenate([host] * reps)[: a.sweeps * a.n_pts] if reps > 1 else host
     pin_in = torch.from_numpy(host_all).pin_memory()
     d_pts = pin_in.to(dev, non_blocking=True)
-    pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path, debug_flags=a.debug_flags)
+    pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path, debug_flags=a.debug_flags,
+                            firing_stride=pkg.synth.SENSORS[a.sensor][0])   # sweeps are stored firing by firing
     out = pr.alloc_outputs(a.sweeps)
     torch.cuda.synchronize()
 

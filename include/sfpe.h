@@ -95,7 +95,12 @@ typedef struct {
   int32_t key_prefix_bits; /* 0 = auto.  Bits of the fp64 range kept in the packed winner key;
                               small values force the exact-compare slow path (tests). */
   int32_t path;            /* 0 = auto, 1 = generic global-scratch kernels, 2 = fused cluster kernel */
-  int32_t reserved[6];   /* must be 0 ([0]: kernel ablation bits for timing experiments, results invalid) */
+  int32_t ablation;        /* must be 0 (kernel ablation bits for timing experiments, -DSFPE_ABLATE builds only; results invalid) */
+  int32_t firing_stride;   /* 0 = 32.  Points per firing (beams of the sensor: 32, 64, 128, 256) when the sweep is
+                              stored firing by firing, as the Velodyne driver delivers it.  A HINT for the fused
+                              kernel's point pass (neighbouring azimuths of a beam are merged per thread): any
+                              value rasterises any cloud to the same result; other values are rounded down. */
+  int32_t reserved[4];     /* must be 0 */
 } sfpe_params;
 
 /* Where the points of a batch live (device memory).  Point p of the batch is at
@@ -270,15 +275,18 @@ SFPE_API const char* sfpe_last_path(const sfpe_ctx* ctx);
 /* Profiling hook (no reference counterpart; the reference's analogue is the cProfile toggle at
  * team_sf_rosnode/scripts/lidar_predict.py:21-23).  enable != 0: the fused kernel accumulates SM
  * cycles per phase (and the counters are reset); 0: off.  sfpe_phase_cycles synchronises the
- * device and returns the sums over all CTAs: out8[0..7] = key init, point pass, deferred fp64
- * pass, range-scan resolve, BEV tile compose, BEV exact redo, BEV tile write, unused. */
+ * device and returns the sums over all CTAs: out[0..SFPE_N_PHASES-1] = key init, point pass,
+ * deferred fp64 pass, range-scan resolve, BEV tile compose, BEV exact redo, BEV line write-out,
+ * exact settlement, wait for the store warp, BEV line list, write-out of the last frames by all
+ * warps, unused. */
+#define SFPE_N_PHASES 12
 SFPE_API int sfpe_phase_profile(sfpe_ctx* ctx, int32_t enable);
 /* Self-test of the fused kernel's fp32 fast path on n packed float32 x,y,z,intensity points
  * (device): out4[k] = largest deviation of the fp32 cell coordinate from its fp64 definition
  * divided by the guard band that protects it (k = 0 azimuth column, 1 elevation row, 2 range
  * bucket, 3 BEV bin).  A value < 1 means every fp32 decision taken was provably exact. */
 SFPE_API int sfpe_selftest_fastpath(sfpe_ctx* ctx, const float* d_xyzi, int64_t n, double* out4);
-SFPE_API int sfpe_phase_cycles(sfpe_ctx* ctx, int64_t* out8);
+SFPE_API int sfpe_phase_cycles(sfpe_ctx* ctx, int64_t* out /* [SFPE_N_PHASES] */);
 
 #ifdef __cplusplus
 }

@@ -28,7 +28,8 @@ class Params(C.Structure):
         ("extrinsic", C.c_double * 12),
         ("slice_edges", C.c_double * (MAX_SLICES + 1)),
         ("key_prefix_bits", C.c_int32), ("path", C.c_int32),
-        ("reserved", C.c_int32 * 6),
+        ("ablation", C.c_int32), ("firing_stride", C.c_int32),
+        ("reserved", C.c_int32 * 4),
     ]
 
 

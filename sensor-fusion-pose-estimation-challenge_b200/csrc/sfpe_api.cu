@@ -299,7 +299,9 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.rowbits = fx.cqueue + (size_t)fx.grid * fx.per_cta * 12;
     fx.counter = fx.rowbits + (size_t)fx.grid * geo.rows_cap * 2;
     fs.frame0 = 0; fs.n_frames = n_frames;
-    fx.debug = c->params.reserved[0];
+    fx.debug = c->params.ablation;
+    fx.spw_log2 = 0;
+    for (int fsd = c->params.firing_stride; fsd >= 64 && fx.spw_log2 < 3; fsd >>= 1) ++fx.spw_log2;
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;
     CK(c, launch_fused(g, src, fs, c->scratch, out, fx, st, &c->launches));
     c->last_path = "fused";
@@ -415,24 +417,24 @@ extern "C" int sfpe_phase_profile(sfpe_ctx* c, int32_t enable) {
     int sms = 0;
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
     c->prof_grid = sms;
-    CK(c, cudaMalloc((void**)&c->d_prof, (size_t)sms * 8 * sizeof(long long)));
+    CK(c, cudaMalloc((void**)&c->d_prof, (size_t)sms * SFPE_N_PHASES * sizeof(long long)));
   }
-  CK(c, cudaMemset(c->d_prof, 0, (size_t)c->prof_grid * 8 * sizeof(long long)));
+  CK(c, cudaMemset(c->d_prof, 0, (size_t)c->prof_grid * SFPE_N_PHASES * sizeof(long long)));
   return SFPE_OK;
 }
 
 extern "C" int sfpe_phase_cycles(sfpe_ctx* c, int64_t* out8) {
   if (!c || !out8) return SFPE_ERR_INVALID_ARG;
-  for (int i = 0; i < 8; ++i) out8[i] = 0;
+  for (int i = 0; i < SFPE_N_PHASES; ++i) out8[i] = 0;
   if (!c->d_prof) return SFPE_OK;
   CK(c, cudaSetDevice(c->device));
   CK(c, cudaDeviceSynchronize());
-  long long* h = (long long*)malloc((size_t)c->prof_grid * 8 * sizeof(long long));
+  long long* h = (long long*)malloc((size_t)c->prof_grid * SFPE_N_PHASES * sizeof(long long));
   if (!h) return SFPE_ERR_NOMEM;
-  cudaError_t e = cudaMemcpy(h, c->d_prof, (size_t)c->prof_grid * 8 * sizeof(long long), cudaMemcpyDeviceToHost);
+  cudaError_t e = cudaMemcpy(h, c->d_prof, (size_t)c->prof_grid * SFPE_N_PHASES * sizeof(long long), cudaMemcpyDeviceToHost);
   if (e == cudaSuccess)
     for (int b = 0; b < c->prof_grid; ++b)
-      for (int i = 0; i < 8; ++i) out8[i] += h[b * 8 + i];
+      for (int i = 0; i < SFPE_N_PHASES; ++i) out8[i] += h[b * SFPE_N_PHASES + i];
   free(h);
   CK(c, e);
   return SFPE_OK;

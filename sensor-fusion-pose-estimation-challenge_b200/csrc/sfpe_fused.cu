@@ -38,7 +38,7 @@ constexpr int IDX_BITS32 = 18;                       // point index bits of the 
 constexpr unsigned IDX_MASK32 = (1u << IDX_BITS32) - 1u;
 constexpr unsigned KEY32_EMPTY = 0xFFFFFFFFu;
 constexpr long long FUSED_MAX_N = (1ll << IDX_BITS32) - 1;  // idx 2^18-1 is reserved for EMPTY
-constexpr int SMEM_MISC_WORDS = 256;                 // LUT (129 floats) | 16 counters | 16 profile words | bucket counts | rings
+constexpr int SMEM_MISC_WORDS = 256;                 // LUT (132 floats) | 16 counters | 16 profile words | bucket counts | rings
 constexpr int ENTRY_BATCH = 3;                       // 16-byte entry loads (4 entries each) in flight per thread (S2 compose)
 constexpr int SMEM_LIMIT = 232448;                   // 227 KB opt-in maximum per CTA
 
@@ -50,6 +50,9 @@ __device__ __forceinline__ unsigned long long l2_policy_evict_last() {
 }
 __device__ __forceinline__ void st_u32_hint(unsigned* ptr, unsigned v, unsigned long long pol) {
   asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(ptr), "r"(v), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void st_u32x4_hint(uint4* ptr, const uint4 v, unsigned long long pol) {
+  asm volatile("st.global.L2::cache_hint.v4.u32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(ptr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
 }
 __device__ __forceinline__ unsigned ld_u32_hint(const unsigned* ptr, unsigned long long pol) {
   unsigned v;
@@ -88,6 +91,26 @@ __device__ __forceinline__ void note_collision(uint2* __restrict__ cq, unsigned*
   }
 }
 
+// the same for the four points of a point-pass step: one reservation per thread
+__device__ __forceinline__ void note_collisions4(uint2* __restrict__ cq, unsigned* misc, const int (&cell)[4],
+                                                 const unsigned (&key)[4], const unsigned (&old)[4]) {
+  unsigned nrec = 0u, hit = 0u;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const bool c = old[u] != KEY32_EMPTY && ((old[u] ^ key[u]) >> IDX_BITS32) == 0;
+    if (c) { hit |= 1u << u; nrec += key[u] < old[u] ? 2u : 1u; }
+  }
+  if (hit) {
+    unsigned pos = atomicAdd(&misc[7], nrec);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (hit & (1u << u)) {
+        cq[pos++] = make_uint2((unsigned)cell[u], key[u] & IDX_MASK32);
+        if (key[u] < old[u]) cq[pos++] = make_uint2((unsigned)cell[u], old[u] & IDX_MASK32);
+      }
+  }
+}
+
 // candidate (point idx, coordinates v) against the holder of *addr: `cur` is the key read
 // before and hv the coordinates of ITS point (both loaded by the caller, so that the loads of
 // several candidates are in flight together); reloaded only when the holder changes under us.
@@ -113,39 +136,36 @@ __device__ __forceinline__ void settle_candidate(const float4* __restrict__ fram
 // equivalent).  Fast form: add, and take it back if the byte was already >= 128.  A byte can
 // only wrap into its neighbour if some add observes it at >= 192 first (>= 64 adds in flight on
 // one cell); that observation is returned so the caller can redo the tile with the exact form.
-__device__ __forceinline__ bool tile_count(unsigned* tile, unsigned r) {
-  const unsigned sh = (r & 3u) * 8u;
-  const unsigned ob = (atomicAdd(tile + (r >> 2), 1u << sh) >> sh) & 0xFFu;
-  if (ob >= 128u) atomicSub(tile + (r >> 2), 1u << sh);
-  return ob >= 192u;
-}
 // The same in two steps, so that many counts can be in flight per thread.  issue: r = position
 // in the tile (>= T: not in this tile); returns (r | TC_VALID | previous byte << 24) or 0.
 // finish: an add on a byte that was already >= 128 is undone, and the >= 192 observation reported.
 constexpr unsigned TC_VALID = 1u << 23;
 // Every counted cell also marks its 128-byte output line (32 cells) in the tile's line flags: one
 // byte per line, plain stores (everybody writes the same 1).
-__device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned char* lf, unsigned r, unsigned T) {
+// An entry is a run: tile coordinate of the cell in the low 30 bits, points - 1 (0..3) on top.
+constexpr unsigned ENTRY_CELL = 0x3FFFFFFFu;
+__device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned char* lf, unsigned e, unsigned tlo, unsigned T) {
+  const unsigned r = (e & ENTRY_CELL) - tlo;
   if (r >= T) return 0u;
   lf[r >> 5] = 1;
   const unsigned sh = (r & 3u) * 8u;
-  const unsigned ob = (atomicAdd(tile + (r >> 2), 1u << sh) >> sh) & 0xFFu;
-  return r | TC_VALID | (ob << 24);
+  const unsigned ob = (atomicAdd(tile + (r >> 2), ((e >> 30) + 1u) << sh) >> sh) & 0xFFu;
+  return r | ((e >> 30) << 21) | TC_VALID | (ob << 24);   // r < 2^17 (T <= 2^17)
 }
 __device__ __forceinline__ bool tile_count_finish(unsigned* tile, unsigned packed) {
   if (!(packed & TC_VALID)) return false;
-  const unsigned ob = packed >> 24, r = packed & (TC_VALID - 1u);
+  const unsigned ob = packed >> 24, r = packed & 0x1FFFFFu;
   if (ob < 128u) return false;
-  atomicSub(tile + (r >> 2), 1u << ((r & 3u) * 8u));
+  atomicSub(tile + (r >> 2), (((packed >> 21) & 3u) + 1u) << ((r & 3u) * 8u));
   return ob >= 192u;
 }
-// Exact form: CAS loop that never lets a byte pass 128.  Returns true for the first arrival.
-__device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r) {
+// Exact form: CAS loop that never adds to a byte that has reached 128.  Returns true for the first arrival.
+__device__ __forceinline__ bool tile_count_exact(unsigned* tile, unsigned r, unsigned c) {
   const unsigned sh = (r & 3u) * 8u;
   unsigned* a = tile + (r >> 2);
   unsigned cur = *reinterpret_cast<volatile unsigned*>(a);
   while (((cur >> sh) & 0xFFu) < 128u) {
-    const unsigned prev = atomicCAS(a, cur, cur + (1u << sh));
+    const unsigned prev = atomicCAS(a, cur, cur + (c << sh));
     if (prev == cur) return ((cur >> sh) & 0xFFu) == 0u;
     cur = prev;
   }
@@ -202,7 +222,7 @@ __device__ __forceinline__ void st_cs_f32x8(float* p, const float4 a, const floa
 }
 
 // four u8 counts -> density values; the table has an entry for every value a settled count byte
-// can hold (0..128: the saturating add never leaves a byte above 128)
+// can hold (0..131: the saturating add of a run of <= 4 points never leaves a byte above 127 + 4)
 __device__ __forceinline__ float4 lut4(const float* lut, unsigned word) {
   float4 v;
   v.x = lut[word & 0xFFu]; v.y = lut[(word >> 8) & 0xFFu];
@@ -222,9 +242,10 @@ struct FusedArgs {
   int range_vec4;      // H*W % 4 == 0 and 16-byte aligned range / winner buffers: vector resolve
   float* bev;
   int* status; int* dropped;
-  int tile_log2;       // BEV cells per shared-memory tile = 1 << tile_log2 (>= 6)
+  int spw_log2;        // log2(beams per firing / 32): the point pass walks the sweep in blocks of four firings
+  int tile_log2;       // BEV cells per shared-memory tile = 1 << tile_log2 (>= 10)
   int tiles_per_bucket, n_buckets;
-  long long* prof;     // optional [grid][8] accumulated SM cycles per phase (sfpe_phase_cycles)
+  long long* prof;     // optional [grid][SFPE_N_PHASES] accumulated SM cycles per phase (sfpe_phase_cycles)
   unsigned* counter;   // frames claimed so far (dynamic assignment), zeroed before the launch
   unsigned* rowbits;   // [grid][2][rows_cap / 4] parked: one byte per 1 KB output row, bit l = its 128-byte line l is non-empty
   long long rows_cap;
@@ -355,8 +376,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   //       [4] frames whose BEV image the store warp has written, [5] tiles parked so far (all frames),
   //       [6] frames claimed so far, [7] collision records, [9] claim broadcast, [10] parked sectors of the
   //       frame in S2, [11] store-warp pacing window, [12..15] claim ring: frame + 1 (~0: no more frames),
-  //       [16..31] phase cycles, [32..95] entries per bucket, [96..99] ring: misc[5] when the frame was
-  //       claimed, [100..101] group cursor of the frame being written (by frame parity)
+  //       [16..39] phase cycles, [40..103] entries per bucket, [104..107] ring: misc[5] when the frame was
+  //       claimed, [108..109] block cursor of the frame being written (by frame parity)
   unsigned* const misc = smem + main_words + 136;
   const int tid = threadIdx.x;
   const int hw = g.H * g.W;
@@ -364,12 +385,12 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   const bool do_bev = g.enable_bev && a.bev;
   const int f_end = a.fs.frame0 + a.fs.n_frames;
   const bool store_active = do_bev && !DBG(1);   // is there a BEV image to write?
-  if (tid < 129) lut[tid] = (float)a.lut64[min(tid, 64)];
+  if (tid < 132) lut[tid] = (float)a.lut64[min(tid, 64)];
   if (tid < 16) misc[tid] = 0u;
-  if (tid >= 96 && tid < 104) misc[tid] = 0u;
-  long long* const prof_acc = reinterpret_cast<long long*>(misc + 16);   // [8], thread 0 only
+  if (tid >= 104 && tid < 112) misc[tid] = 0u;
+  long long* const prof_acc = reinterpret_cast<long long*>(misc + 16);   // [SFPE_N_PHASES], thread 0 only
   if (tid == 0)
-    for (int k = 0; k < 8; ++k) prof_acc[k] = 0;
+    for (int k = 0; k < SFPE_N_PHASES; ++k) prof_acc[k] = 0;
   __syncthreads();   // the only CTA-wide barrier: the roles part here
 
   // ======================================================================== store warp
@@ -381,8 +402,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       while ((int)(ld_acquire_smem(&misc[6]) - (k + 1u)) < 0) __nanosleep(1000);
       const unsigned c = *reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]);
       if (c == ~0u) return;
-      const BevJob j = make_bev_job(a, cells, (int)c - 1, k, *reinterpret_cast<volatile unsigned*>(&misc[96 + (k & 3u)]));
-      bev_write_frame(j, &misc[100 + (k & 1u)], misc, sl, true);
+      const BevJob j = make_bev_job(a, cells, (int)c - 1, k, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k & 3u)]));
+      bev_write_frame(j, &misc[108 + (k & 1u)], misc, sl, true);
       __syncwarp();
       if (sl == 0) st_release_smem(&misc[4], k + 1u);   // the parked bitmaps of frame k may be overwritten
     }
@@ -390,7 +411,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
   // ======================================================================== compute warps
   unsigned* const my_buckets = a.entries + (size_t)blockIdx.x * a.n_buckets * a.per_cta;   // [bucket][per_cta]
-  unsigned* const bcnt = misc + 32;   // entries per bucket [MAX_BUCKETS]
+  unsigned* const bcnt = misc + 40;   // entries per bucket [MAX_BUCKETS]
   const int lane = tid & 31;
   const unsigned per_cta32 = (unsigned)a.per_cta;
   const unsigned lane_lt = (1u << lane) - 1u;
@@ -412,7 +433,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       misc[9] = c;
       if (store_active) {
         *reinterpret_cast<volatile unsigned*>(&misc[12 + (frames_done & 3u)]) = c;
-        *reinterpret_cast<volatile unsigned*>(&misc[96 + (frames_done & 3u)]) = misc[5];
+        *reinterpret_cast<volatile unsigned*>(&misc[104 + (frames_done & 3u)]) = misc[5];
         st_release_smem(&misc[6], frames_done + 1u);
       }
     }
@@ -434,32 +455,45 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       if (tid < (hw & 3)) keys[(hw & ~3) + tid] = KEY32_EMPTY;
     }
     if (tid < 4) misc[tid] = 0u;
-    if (tid >= 32 && tid < 32 + MAX_BUCKETS) misc[tid] = 0u;
+    if (tid >= 40 && tid < 40 + MAX_BUCKETS) misc[tid] = 0u;
     if (tid == 0) {
       misc[7] = 0u; misc[8] = 0u; misc[9] = 0u;
       misc[11] = 1u;               // the point pass hardly uses the path to L2: store-warp window open
     }
-    // the first two S1 iterations of points are pulled into L2 while the keys are initialised
-    for (long long l = tid; l * 8 < n && l < 3 * (4 * CT / 8); l += CT) prefetch_l2(fp + l * 8);
+    // ---- S1: one pass over the points
+    // (32-bit indices: n < 2^18 on this path.)  A warp step takes four consecutive FIRINGS of 32
+    // beams: lane = beam, and a thread's four points are the same beam at four consecutive azimuths
+    // (a.spw_log2: beams per firing = 32 << spw_log2, a hint -- any value rasterises any cloud
+    // correctly).  Such neighbours mostly fall into the same BEV cell and almost always into the same
+    // BEV tile, so a thread merges them into runs (cell, count) and the warp appends all its runs
+    // with ONE match / shared-memory atomic.  The points of the next step are loaded while the
+    // current ones are rasterised, into the other of two register sets (no copies).
+    const int n32 = (int)n;
+    const int spw_log2 = a.spw_log2, fstride = 32 << spw_log2;          // points per firing
+    const int n_steps = ((n32 + 4 * fstride - 1) / (4 * fstride)) << spw_log2;   // warp steps of this frame
+    // first point of warp step q: block of 4 firings (q >> spw_log2), 32-beam part (q & (spw - 1))
+    auto step_base = [&](int q) { return (q >> spw_log2) * 4 * fstride + ((q & ((1 << spw_log2) - 1)) << 5); };
+    auto prefetch_step = [&](int q) {   // the 16 lines (4 firings x 512 bytes) of step q
+      const int i = step_base(q) + (lane >> 2) * fstride + (lane & 3) * 8;
+      if (lane < 16 && q < n_steps && i < n32) prefetch_l2(fp + i);
+    };
+    // the first three steps of every warp are pulled into L2 while the keys are initialised
+#pragma unroll
+    for (int k = 0; k < 3; ++k) prefetch_step((tid >> 5) + k * CW);
     compute_sync();
     PROF_STAMP(0);
 
-    // ---- S1: one pass over the points
-    // (32-bit indices: n < 2^18 on this path.)  The points of the next iteration are loaded while
-    // the current one is rasterised, into the other of two register sets (no copies).
-    const int n32 = (int)n;
-    auto load4 = [&](float4 (&v)[4], int i0) {
+    auto load4 = [&](float4 (&v)[4], int q) {
+      const int i0 = step_base(q) + lane;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * CT + tid;
+        const int i = i0 + u * fstride;
         v[u] = i < n32 ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     };
-    auto rasterise4 = [&](const float4 (&v)[4], const int i0) {
-      {  // L2 prefetch three iterations ahead (one 128-byte line = 8 points per thread)
-        const int l = i0 + 3 * 4 * CT + tid * 8;
-        if (tid < 4 * CT / 8 && l < n32 && !DBG(64)) prefetch_l2(fp + l);
-      }
+    auto rasterise4 = [&](const float4 (&v)[4], const int q) {
+      if (!DBG(64)) prefetch_step(q + 3 * CW);   // L2 prefetch three steps ahead
+      const int i0 = step_base(q) + lane;
       // Per point, branch-free (so that the four points of a thread interleave): every decision
       // -- range-scan cell, range bucket, BEV bins -- is made in fp32 and PROVEN by its guard
       // band; a point with any unproven decision is deferred as a whole to S1b (fp64).
@@ -470,7 +504,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       bool defer[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * CT + tid;
+        const int i = i0 + u * fstride;
         const bool valid = i < n32;
         const float x = v[u].x, y = v[u].y, z = v[u].z;
         bool undecided = false;
@@ -515,12 +549,28 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         if (!valid || defer[u] || !g.enable_range) cell[u] = -1;
         if (defer[u]) bb[u] = NO_BUCKET;
       }
+      if (defer[0] | defer[1] | defer[2] | defer[3]) {   // rare: one reservation per thread
+        unsigned pos = atomicAdd(&misc[0], (unsigned)defer[0] + (unsigned)defer[1] + (unsigned)defer[2] + (unsigned)defer[3]);
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (defer[u]) my_queue[atomicAdd(&misc[0], 1u)] = (unsigned)(i0 + u * CT + tid);
-      // BEV entries are appended to the bucket of their tile, one shared-memory atomic per
-      // (warp, bucket): lanes with the same bucket elect a leader that reserves the slots
+        for (int u = 0; u < 4; ++u)
+          if (defer[u]) my_queue[pos++] = (unsigned)(i0 + u * fstride);
+      }
+      // the four shared-memory atomics of the range scan go out back to back; their results are
+      // looked at after the BEV append (whose warp-wide steps they overlap)
+      unsigned old[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !DBG(32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
+      // BEV entries.  Neighbouring points of the thread in the same cell become one run (the count
+      // - 1 rides in the two top bits of the entry).  Each run is appended to the bucket of its tile
+      // with one shared-memory atomic per (warp, bucket): lanes with the same bucket elect a leader
+      // that reserves the slots (warp-aggregated: __match_any_sync).
       if (do_bev && !DBG(16)) {
+        unsigned cnt[4] = {0u, 0u, 0u, 0u};   // run length - 1
+#pragma unroll
+        for (int u = 3; u >= 1; --u) {
+          const bool same = bb[u] != NO_BUCKET && bb[u - 1] != NO_BUCKET && be[u] == be[u - 1];
+          if (same) { cnt[u - 1] += cnt[u] + 1u; bb[u] = NO_BUCKET; }
+        }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const unsigned m = __match_any_sync(0xFFFFFFFFu, bb[u]);
@@ -528,25 +578,23 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           unsigned slot = 0u;
           if (lane == leader && bb[u] != NO_BUCKET) slot = atomicAdd(&bcnt[bb[u]], (unsigned)__popc(m));
           slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + (unsigned)__popc(m & lane_lt);
-          if (bb[u] != NO_BUCKET) st_u32_hint(my_buckets + ((unsigned)bb[u] * per_cta32 + slot), be[u], keep);
+          if (bb[u] != NO_BUCKET) st_u32_hint(my_buckets + ((unsigned)bb[u] * per_cta32 + slot), be[u] | (cnt[u] << 30), keep);
         }
       }
-      // the four shared-memory atomics go out back to back; their results are looked at afterwards
-      unsigned old[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !DBG(32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) note_collision(my_cq, misc, cell[u], key[u], old[u]);
+      note_collisions4(my_cq, misc, cell, key, old);
     };
     {
       float4 va[4], vb[4];
-      load4(va, 0);
-      for (int i0 = 0; i0 < n32; i0 += 8 * CT) {
-        load4(vb, i0 + 4 * CT);
-        rasterise4(va, i0);
-        if (i0 + 4 * CT >= n32) break;
-        load4(va, i0 + 8 * CT);
-        rasterise4(vb, i0 + 4 * CT);
+      int q = tid >> 5;
+      load4(va, q);
+      while (q < n_steps) {
+        load4(vb, q + CW);
+        rasterise4(va, q);
+        q += CW;
+        if (q >= n_steps) break;
+        load4(va, q + CW);
+        rasterise4(vb, q);
+        q += CW;
       }
     }
     compute_sync();
@@ -807,11 +855,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           while ((int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) __nanosleep(200);
           misc[11] = 1u;
         }
-        misc[100 + par] = 0u;
+        misc[108 + par] = 0u;
       }
-#ifdef SFPE_PROFX
-      PROF_STAMP(0);
-#endif
+      PROF_STAMP(8);
       for (int w = tid; w < ((tw + lbw) >> 2); w += CT) reinterpret_cast<uint4*>(tile)[w] = make_uint4(0u, 0u, 0u, 0u);   // tw, lbw: multiples of 4
       compute_sync();
       const unsigned span_all = (unsigned)cells + head;
@@ -854,10 +900,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           // stage 1: all counts go out back to back; every slot keeps (position | valid | old byte << 24)
 #pragma unroll
           for (int u = 0; u < ENTRY_BATCH; ++u) {
-            e[u].x = tile_count_issue(tile, lf, e[u].x - tlo, (unsigned)T);
-            e[u].y = tile_count_issue(tile, lf, e[u].y - tlo, (unsigned)T);
-            e[u].z = tile_count_issue(tile, lf, e[u].z - tlo, (unsigned)T);
-            e[u].w = tile_count_issue(tile, lf, e[u].w - tlo, (unsigned)T);
+            e[u].x = tile_count_issue(tile, lf, e[u].x, tlo, (unsigned)T);
+            e[u].y = tile_count_issue(tile, lf, e[u].y, tlo, (unsigned)T);
+            e[u].z = tile_count_issue(tile, lf, e[u].z, tlo, (unsigned)T);
+            e[u].w = tile_count_issue(tile, lf, e[u].w, tlo, (unsigned)T);
           }
           // stage 2: saturation fix-ups (rare)
 #pragma unroll
@@ -878,9 +924,11 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           compute_sync();
           const unsigned* const bucket = my_buckets + (size_t)bkt * a.per_cta;
           for (unsigned i = tid; i < cnt; i += CT) {
-            const unsigned r = __ldcg(bucket + i) - tlo;
-            if (r < (unsigned)T) { tile_count_exact(tile, r); lf[r >> 5] = 1; }
+            const unsigned e = __ldcg(bucket + i);
+            const unsigned r = (e & ENTRY_CELL) - tlo;
+            if (r < (unsigned)T) { tile_count_exact(tile, r, (e >> 30) + 1u); lf[r >> 5] = 1; }
           }
+
           compute_sync();
           PROF_STAMP(5);
         }
@@ -933,9 +981,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             }
           }
           compute_sync();
-#ifdef SFPE_PROFX
-          PROF_STAMP(2);
-#endif
+          PROF_STAMP(9);
           if (tid == 0) misc[11] = 0u;   // the write-out stores to global memory: store-warp window closed
           const unsigned wn = misc[10];
           float* const bp = a.bev + (long long)f * cells - head;   // tile coordinate 0
@@ -976,13 +1022,13 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     if (tid == 0) misc[11] = 2u;
     for (unsigned k = frames_done >= 2u ? frames_done - 2u : 0u; k < frames_done; ++k) {
       const int fk = (int)*reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]) - 1;
-      const BevJob j = make_bev_job(a, cells, fk, k, *reinterpret_cast<volatile unsigned*>(&misc[96 + (k & 3u)]));
-      bev_write_frame(j, &misc[100 + (k & 1u)], misc, lane, false);
+      const BevJob j = make_bev_job(a, cells, fk, k, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k & 3u)]));
+      bev_write_frame(j, &misc[108 + (k & 1u)], misc, lane, false);
     }
-    PROF_STAMP(5);
+    PROF_STAMP(10);
   }
   if (a.prof && tid == 0)
-    for (int k = 0; k < 8; ++k) a.prof[(size_t)blockIdx.x * 8 + k] += prof_acc[k];
+    for (int k = 0; k < SFPE_N_PHASES; ++k) a.prof[(size_t)blockIdx.x * SFPE_N_PHASES + k] += prof_acc[k];
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1019,7 +1065,7 @@ bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, l
   if (!packed || g.use_extrinsic || g.n_slices || max_n > FUSED_MAX_N) return false;
   if (g.enable_range && (out.range_dtype != 0 || g.H * g.W > main_words_max())) return false;
   if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts)) return false;
-  if (g.enable_bev && (long long)g.nbx * g.nby > 0x7FFFFF00ll) return false;
+  if (g.enable_bev && (long long)g.nbx * g.nby > 0x3FF00000ll) return false;   // entries: 30-bit tile coordinate + 2-bit run length
   return g.enable_range || g.enable_bev;
 }
 
@@ -1053,6 +1099,7 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.range = (float*)out.range; a.range_layout = out.range_layout; a.winner = out.range_winner;
   a.bev = (float*)out.bev;
   a.status = out.status; a.dropped = out.dropped;
+  a.spw_log2 = fx.spw_log2;
   a.tile_log2 = geo.tile_log2; a.tiles_per_bucket = geo.tiles_per_bucket; a.n_buckets = geo.n_buckets;
   a.range_vec4 = ((g.H * g.W) & 3) == 0 && ((uintptr_t)out.range & 15) == 0 && ((uintptr_t)out.range_winner & 15) == 0;
   a.prof = fx.prof;

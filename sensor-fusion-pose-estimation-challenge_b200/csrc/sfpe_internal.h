@@ -1,5 +1,6 @@
 // Internal host/device interface between the C-ABI translation unit and the kernel files.
 #pragma once
+#include "../../include/sfpe.h"
 #include "sfpe_common.cuh"
 
 namespace sfpe {
@@ -84,7 +85,8 @@ struct FusedScratch {
   unsigned* rowbits;   // [grid][2][rows_cap]: parked BEV row bitmaps (non-empty sectors)
   long long per_cta;   // >= max points of a frame
   int grid;            // CTAs (<= SMs)
-  long long* prof;     // optional [grid][8] phase cycle accumulators
+  int spw_log2;        // log2(firing stride / 32), 0..3
+  long long* prof;     // optional [grid][SFPE_N_PHASES] phase cycle accumulators
   int debug;           // sfpe_params.reserved[0]: ablation bits (-DSFPE_ABLATE builds only)
 };
 struct FusedGeom { int tile_log2, tiles_per_bucket, n_buckets, s2_words; long long rows_cap; };

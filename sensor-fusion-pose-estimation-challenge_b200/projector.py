@@ -22,9 +22,11 @@ def _torch():
 
 class LidarProjector:
     def __init__(self, device=0, bev_res=(0.2, 0.2), max_range=120, enable_range=True, enable_bev=True,
-                 extrinsic=None, slice_edges=None, key_prefix_bits=0, path=0, debug_flags=0, **grid):
+                 extrinsic=None, slice_edges=None, key_prefix_bits=0, path=0, debug_flags=0, firing_stride=0, **grid):
         """bev_res = (res_y, res_x) like the reference's `res` tuple
-        (birds_eye_view_generator.py:43 uses res[1] for x and res[0] for y)."""
+        (birds_eye_view_generator.py:43 uses res[1] for x and res[0] for y).
+        firing_stride: beams per firing (32 / 64 / 128) when sweeps arrive firing by firing -- a
+        performance hint for the fused kernel, never changes a result."""
         self.lib = _lib.load()
         p = _lib.default_params()
         p.bev_res_y, p.bev_res_x = float(bev_res[0]), float(bev_res[1])
@@ -50,7 +52,8 @@ class LidarProjector:
             p.n_slices = len(se) - 1
             for i, v in enumerate(se):
                 p.slice_edges[i] = v
-        p.reserved[0] = int(debug_flags)
+        p.ablation = int(debug_flags)
+        p.firing_stride = int(firing_stride)   # beams per firing of a firing-ordered sweep (performance hint only)
         p.key_prefix_bits = int(key_prefix_bits)
         p.path = int(path)
         self.params = p
@@ -81,7 +84,8 @@ class LidarProjector:
     def last_path(self):
         return self.lib.sfpe_last_path(self._ctx).decode()
 
-    PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo_and_tail_write", "bev_park", "settle")
+    PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo", "bev_line_write", "settle",
+              "wait_store_warp", "bev_line_list", "tail_write", "unused")
 
     def phase_profile(self, enable=True):
         """Switch the fused kernel's per-phase SM-cycle counters on (and reset them) or off."""
@@ -89,7 +93,7 @@ class LidarProjector:
 
     def phase_cycles(self):
         """dict phase -> SM cycles summed over all CTAs since phase_profile(True)."""
-        buf = (C.c_int64 * 8)()
+        buf = (C.c_int64 * len(self.PHASES))()
         _lib.check(self.lib.sfpe_phase_cycles(self._ctx, buf), self._ctx)
         return dict(zip(self.PHASES, [int(v) for v in buf]))
 

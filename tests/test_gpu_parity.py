@@ -84,7 +84,7 @@ def _run_batch(pkg, sweeps, ragged=True, **kw):
     offs[1:] = np.cumsum([len(s) for s in sweeps])
     counts = kw.pop("counts", True)
     proj_kw = {k: kw.pop(k) for k in list(kw) if k in ("bev_res", "max_range", "key_prefix_bits", "path",
-                                                       "extrinsic", "slice_edges")}
+                                                       "extrinsic", "slice_edges", "firing_stride")}
     pr = pkg.LidarProjector(device=0, **proj_kw)
     d = torch.from_numpy(allp).cuda() if len(allp) else torch.zeros((1, 4), dtype=torch.float32, device="cuda")
     if ragged:
@@ -427,10 +427,10 @@ def test_fused_equals_generic_randomized(pkg, synth, seed):
 
 
 # ---------------------------------------------------------------- the benchmarked launch shape
-def _device_batch(pkg, pts_all, n_frames, n_pts, path, bev_res):
+def _device_batch(pkg, pts_all, n_frames, n_pts, path, bev_res, firing_stride=0):
     """One project() call over n_frames uniform sweeps already on the device; outputs stay there."""
     import torch
-    pr = pkg.LidarProjector(device=0, bev_res=bev_res, path=path)
+    pr = pkg.LidarProjector(device=0, bev_res=bev_res, path=path, firing_stride=firing_stride)
     out = pr.project(pts_all, n_frames=n_frames, uniform_n=n_pts, winner=True)
     torch.cuda.synchronize()
     assert pr.last_path == ("fused" if path == 2 else "generic")
@@ -451,7 +451,7 @@ def test_fused_full_size_batches_like_the_bench(pkg, synth, sensor, res, n_frame
               for i in range(n_frames)]
     n_pts = len(sweeps[0])
     d = torch.from_numpy(np.concatenate(sweeps)).cuda()
-    a = _device_batch(pkg, d, n_frames, n_pts, 2, (res, res))
+    a = _device_batch(pkg, d, n_frames, n_pts, 2, (res, res), firing_stride=synth.SENSORS[sensor][0])   # as bench.py does
     b = _device_batch(pkg, d, n_frames, n_pts, 1, (res, res))
     for k in ("range", "winner", "bev", "status", "dropped"):
         assert torch.equal(a[k], b[k]), k
@@ -490,6 +490,22 @@ def test_fused_rewrites_every_bev_byte(pkg, synth):
         for f in (0, 4, 8):
             _check_density(out["bev"][f].cpu().numpy(), lo.bev_density(_P(sweeps[f]), (0.2, 0.2), 120))
     pr.close()
+
+
+@pytest.mark.parametrize("stride", [0, 32, 64, 128, 256, 48])
+def test_fused_firing_stride_is_only_a_hint(pkg, synth, stride):
+    """sfpe_params.firing_stride tells the fused kernel's point pass how the sweep is laid out; right, wrong
+    or absurd, every output must stay the same (ragged frames, firing-ordered and shuffled, three sensors)."""
+    sweeps = [synth.make_sweep("hdl32", seed=7100), synth.make_sweep("hdl64", seed=7101, shuffle=True),
+              synth.make_sweep("vls128", seed=7102, n_az=500, near_heavy=True), synth.make_sweep("hdl64", seed=7103, dropout=0.2),
+              synth.make_sweep("hdl32", seed=7104, n_az=3), np.zeros((0, 4), np.float32)] * 26        # 156 frames > SM count
+    a = _run_batch(pkg, sweeps, path=2, counts=False, firing_stride=stride)
+    assert a["_path"] == "fused"
+    for f in (0, 1, 2, 3, 4, 5, 150, 151, 152, 153):
+        _check_frame(a, f, sweeps[f])
+    for f in range(6, len(sweeps)):
+        for k in ("range", "winner", "bev", "status", "dropped"):
+            assert np.array_equal(a[k][f], a[k][f % 6]), (f, k)
 
 
 @pytest.mark.parametrize("name", ["hdl32_seed0", "vls128_seed3_near", "edges", "hdl32_seed1_shuffled_dropout"])

@@ -15,6 +15,6 @@ import json,glob
 for f in sorted(glob.glob('gpurun_out/${TAG}_bench*.json')):
     try:
         d=json.load(open(f)); p=d.get('phase_share',{}); t=p.pop('sm_cycles_per_sweep',0)
-        print(f.split('/')[-1], '%.0f sweeps/s frac %.3f verified %s'%(d['value'], d['roofline']['frac'], d.get('verified_frames')), 'cyc %.0f'%t, ' '.join('%s %.0f'%(k[:8],v*t) for k,v in p.items()))
+        print(f.split('/')[-1], '%.0f sweeps/s frac %.3f verified %s'%(d['value'], d['roofline']['frac'], d.get('verified_frames')), 'cyc %.0f'%t, ' '.join('%s %.0f'%(k[:9],v*t) for k,v in p.items()))
     except Exception as e: print(f, 'ERR', e)
 PY
