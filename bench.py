@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 PKG = "sensor-fusion-pose-estimation-challenge_b200"
 
 H, W = 32, 1801
+SENS = {"hdl32": 65536, "hdl64": 120000, "vls128": 249984}
 
 
 def algorithmic_bytes(n_pts, nbx, nby, c_bev=1):
@@ -242,16 +243,28 @@ def run_ours(a):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
+    # ranks of one box share its host: each keeps to its own slice of the cores (the pinned buffers it
+    # allocates below are then first touched there, and its expansion threads stay off the other ranks' cores)
+    local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    if local_world > 1:
+        try:
+            cores = sorted(os.sched_getaffinity(0))
+            per = max(1, len(cores) // local_world)
+            os.sched_setaffinity(0, cores[local * per:(local + 1) * per] or cores)
+        except (AttributeError, OSError):
+            pass
 
     # synthetic batch: distinct seeds per rank; generated on the host, resident in HBM before timing
     pool = min(a.sweeps, a.distinct)
-    host = np.concatenate([pkg.synth.make_sweep(a.sensor, seed=rank * a.sweeps + i) for i in range(pool)])
+    host = np.concatenate([pkg.synth.make_sweep(a.sensor, seed=rank * a.sweeps + i, shuffle=a.shuffle,
+                                                near_heavy=(a.sensor == "vls128")) for i in range(pool)])
     reps = (a.sweeps + pool - 1) // pool
     host_all = np.concatenate([host] * reps)[: a.sweeps * a.n_pts] if reps > 1 else host
     pin_in = torch.from_numpy(host_all).pin_memory()
     d_pts = pin_in.to(dev, non_blocking=True)
     pr = pkg.LidarProjector(device=local, bev_res=(a.bev_res, a.bev_res), path=a.path, debug_flags=a.debug_flags,
-                            firing_stride=pkg.synth.SENSORS[a.sensor][0])   # sweeps are stored firing by firing
+                            firing_stride=pkg.synth.SENSORS[a.sensor][0],   # sweeps are stored firing by firing
+                            slice_edges=SLICE_EDGES[: a.slices + 1] if a.slices else None)
     out = pr.alloc_outputs(a.sweeps)
     torch.cuda.synchronize()
 
@@ -288,9 +301,13 @@ def run_ours(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms = float(t.item())
 
+    sustained = measure_sustained(step, a.sweeps, a.sustain) if (a.sustain > 0 and rank == 0) else None
+    if world > 1:
+        dist.barrier()
+
     # ---- e2e: same metric through the host-buffer API, H2D + D2H inside the timed region
     e2e = None
-    if not a.no_e2e:
+    if not a.no_e2e and not a.slices:
         e2e = run_e2e(a, pkg, pr, pin_in, dev, world)
 
     # ---- optional: per-phase SM cycles of the fused kernel (separate untimed steps)
@@ -318,7 +335,7 @@ def run_ours(a):
     dropped_mean = float(out["dropped"].float().mean().item()) if "dropped" in out else None
     if rank == 0:
         peak, peak_src = measured_peak()
-        bytes_sweep = algorithmic_bytes(a.n_pts, pr.nbx, pr.nby)
+        bytes_sweep = algorithmic_bytes(a.n_pts, pr.nbx, pr.nby, 1 + (a.slices + 1 if a.slices else 0))
         med_ms = float(np.median(step_ms))
         achieved = a.sweeps * bytes_sweep / (med_ms * 1e-3) / 1e9
         value = world * a.sweeps * a.steps / (total_ms * 1e-3)
@@ -338,16 +355,141 @@ def run_ours(a):
                          else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
             "clocks": clocks,
         }
+        if sustained is not None:
+            sustained["frac"] = sustained["sweeps_per_s"] * bytes_sweep / 1e9 / peak
+            line["sustained"] = sustained
+        if a.slices:
+            line["extension"] = "E ON: %d MV3D height slices + intensity of the highest point (parity unpinned: no reference code)" % a.slices
         if phases is not None:
             line["phase_share"] = phases
         if e2e is not None:
             line["e2e"] = e2e
         if not a.no_cpu and world == 1:
             line["cpu_baseline"] = cpu_baseline_block(a)
-        emit(line)
     pr.close()
+    del out, d_pts
+    torch.cuda.empty_cache()
+    if rank == 0:
+        if world == 1 and not a.no_configs and not a.config and not a.debug_flags:
+            # short one-GPU runs of BASELINE.json's other configs, each with its own roofline fraction
+            cfgs = {}
+            cfgs["c2_shuffled_order"] = measure_config(pkg, local, "hdl32", 0.2, 1024, shuffle=True)
+            cfgs["c3_hdl64"] = measure_config(pkg, local, "hdl64", 0.2, 1024)
+            cfgs["c3_hdl64_extension_E_4_slices"] = measure_config(pkg, local, "hdl64", 0.2, 128, slice_edges=SLICE_EDGES)
+            cfgs["c5_vls128_bev_0.05m"] = measure_config(pkg, local, "vls128", 0.05, 296, steps=3)
+            cfgs["c4_streaming_latency"] = measure_streaming(pkg, local)
+            cfgs["dropin_single_sweep"] = measure_dropin(pkg)
+            line["configs"] = cfgs
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------ other configs (BASELINE.json configs[2..4])
+PRESETS = {   # --config: sensor, BEV resolution, sweeps per GPU
+    "c2": ("hdl32", 0.2, 1024),    # configs[1]: the headline
+    "c3": ("hdl64", 0.2, 1024),    # configs[2]: HDL-64E-shaped sweeps, frame-sharded
+    "c5": ("vls128", 0.05, 296),   # configs[4]: 128-beam dense sweeps at 0.05 m BEV (two per SM)
+}
+SLICE_EDGES = (-2.0, -1.0, 0.0, 1.0, 2.0)   # four MV3D height slices for the extension-ON figure
+
+
+def measure_config(pkg, local, sensor, bev_res, sweeps, steps=4, warmup=3, shuffle=False, slice_edges=None, distinct=37):
+    """One short device-resident measurement of another configuration on this GPU (own roofline fraction).
+    `distinct` synthetic sweeps are generated, the batch repeats them (inputs + outputs still exceed the L2)."""
+    import torch
+    n_pts = SENS[sensor]
+    pool = min(sweeps, distinct)
+    host = np.concatenate([pkg.synth.make_sweep(sensor, seed=7000 + i, near_heavy=(sensor == "vls128"), shuffle=shuffle)
+                           for i in range(pool)])
+    reps = (sweeps + pool - 1) // pool
+    d_pts = torch.from_numpy(np.concatenate([host] * reps)[: sweeps * n_pts]).to(torch.device("cuda", local))
+    pr = pkg.LidarProjector(device=local, bev_res=(bev_res, bev_res), firing_stride=pkg.synth.SENSORS[sensor][0],
+                            slice_edges=slice_edges)
+    out = pr.alloc_outputs(sweeps)
+    for _ in range(warmup):
+        pr.project(d_pts, n_frames=sweeps, uniform_n=n_pts, out=out)
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    ev[0].record()
+    for i in range(steps):
+        pr.project(d_pts, n_frames=sweeps, uniform_n=n_pts, out=out)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    ms = float(np.median([ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]))
+    c_bev = 1 if slice_edges is None else len(slice_edges) + 1      # density (+ M height slices + intensity)
+    bytes_sweep = algorithmic_bytes(n_pts, pr.nbx, pr.nby, c_bev)
+    peak, _ = measured_peak()
+    ok = int((out["status"] != 0).sum().item()) == 0
+    res = {"sweeps_per_s": sweeps / (ms * 1e-3), "points_per_s": sweeps * n_pts / (ms * 1e-3), "sweeps": sweeps,
+           "points_per_sweep": n_pts, "bev_res_m": bev_res, "path": pr.last_path, "launch_ms": ms,
+           "algorithmic_bytes_per_sweep": bytes_sweep, "frac": sweeps * bytes_sweep / (ms * 1e-3) / 1e9 / peak,
+           "all_frames_ok": ok}
+    pr.close()
+    del out, d_pts
+    torch.cuda.empty_cache()
+    return res
+
+
+def measure_streaming(pkg, local, n_msgs=1000):
+    """configs[3]: per-sweep latency through the ROS-callback-shaped entry (team_sf_rosnode/scripts/
+    lidar_predict.py:60-75 -> lidar/pipeline.py:10-11 -> train/predict.py:335-343): a PointCloud2 `data` blob in
+    pinned host memory in, the (32,1801,3) float32 network input in pinned host memory out."""
+    sf = pkg.StreamingFrontView(device=local)
+    blobs = [pkg.synth.make_pointcloud2_blob(pkg.synth.make_sweep("hdl32", seed=8000 + i)) for i in range(8)]
+    for i in range(20):
+        sf(blobs[i % 8])
+    lat = []
+    for i in range(n_msgs):
+        t0 = time.perf_counter()
+        sf(blobs[i % 8])
+        lat.append(time.perf_counter() - t0)
+    sf.close()
+    lat = np.array(lat) * 1e3
+    return {"messages": n_msgs, "points_per_message": 65536, "blob_bytes": int(len(blobs[0])),
+            "p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)), "mean_ms": float(lat.mean()),
+            "entry": "StreamingFrontView: pinned blob -> H2D -> sfpe_decode_pointcloud2 -> range scan -> D2H (32,1801,3) f32"}
+
+
+def measure_dropin(pkg, n_calls=15):
+    """The calls the reference's own callers make (train/predict.py:336, extract_rosbag.py:180-187): one
+    float64 (N,5) sweep on the host in, float64 images / the uint8 picture on the host out, per call."""
+    P = pkg.synth.as_reference_array(pkg.synth.make_sweep("hdl32", seed=8100))
+    res = {}
+    for name, fn in (("generate_lidar_2d_front_view", lambda: pkg.generate_lidar_2d_front_view(P)),
+                     ("generate_birds_eye_view_0.2m", lambda: pkg.generate_birds_eye_view(P, 0, (0.2, 0.2)))):
+        for _ in range(3):
+            fn()
+        t = []
+        for _ in range(n_calls):
+            t0 = time.perf_counter()
+            fn()
+            t.append(time.perf_counter() - t0)
+        res[name + "_ms"] = {"median": 1e3 * float(np.median(t)), "best": 1e3 * float(min(t))}
+    res["note"] = "float64 (65536,5) host array in, host arrays out, per call (the generic fp64 path); the reference's " \
+                  "per-call time is cpu_baseline.single_core_ms_per_sweep"
+    return res
+
+
+def measure_sustained(step, sweeps, seconds):
+    """The headline step repeated for >= `seconds` of GPU time (the 20-step figure is a 40 ms burst)."""
+    import torch
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n = 0
+    t0 = time.perf_counter()
+    e0.record()
+    while True:
+        for _ in range(50):
+            step()
+        n += 50
+        torch.cuda.synchronize()
+        if time.perf_counter() - t0 >= seconds:
+            break
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    return {"seconds": ms * 1e-3, "steps": n, "sweeps_per_s": n * sweeps / (ms * 1e-3)}
 
 
 def verify_frames(a, pkg, path_timed, d_pts, out, local, rank, k=8):
@@ -372,14 +514,16 @@ def verify_frames(a, pkg, path_timed, d_pts, out, local, rank, k=8):
 
 def run_e2e(a, pkg, pr, pin_in, dev, world):
     """Host pinned in -> H2D -> kernels -> D2H of every output image, pipelined over chunks on 3 streams.
-    Both BEV transports are timed (the host ends with the same float images either way); the line's value
-    is the faster one and the note names it."""
+    Three result forms are timed: "dense" (float32 BEV over PCIe), "u8" (one byte per BEV cell over PCIe,
+    expanded by host threads into the same float32 image) and "rgb" (the reference's own result type: the
+    uint8 (nb,nb,3) picture of birds_eye_view_generator.py:48-54, expanded on the host from the same bytes);
+    all three deliver the (32,1801,3) float32 range tensor.  The line's value is the fastest; by_result has all."""
     import gc
     import torch
     import torch.distributed as dist
     steps = max(2, min(a.steps, 5))
     res = {}
-    for transport in ("dense", "u8"):
+    for transport in ("dense", "u8", "rgb"):
         hb = pkg.HostBatchPipeline(pr, a.sweeps, a.n_pts, chunk=a.e2e_chunk, bev_transport=transport)
         hb.run(pin_in)            # warm-up (also faults the pinned output pages in)
         hb.synchronize()
@@ -395,18 +539,23 @@ def run_e2e(a, pkg, pr, pin_in, dev, world):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
         res[transport] = {"value": world * a.sweeps * steps / dt, "h2d": int(hb.h2d_bytes), "d2h": int(hb.d2h_bytes),
-                          "chunk": hb.chunk}
+                          "chunk": hb.chunk, "threads": getattr(hb, "unpack_threads", 0)}
         hb.close()
         del hb
         gc.collect()
     best = max(res, key=lambda k: res[k]["value"])
     r = res[best]
+    host_result = {"dense": "float32 BEV density image + float32 (32,1801,3) range tensor",
+                   "u8": "float32 BEV density image (bit-identical, expanded on the host) + float32 range tensor",
+                   "rgb": "uint8 (nb,nb,3) BEV picture (the reference's return type) + float32 range tensor"}
     return {"value": r["value"], "unit": "sweeps/s", "steps": steps,
             "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"], "bev_transport": best,
             "by_transport": {k: round(v["value"], 1) for k, v in res.items()},
-            "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; dense: float BEV over PCIe; "
-                    "u8: one byte per BEV cell over PCIe, expanded into the same pinned float image by host "
-                    "threads inside the timed region (bit-identical result)" % r["chunk"]}
+            "by_result": {k: {"sweeps_per_s": round(v["value"], 1), "host_result": host_result[k],
+                              "d2h_bytes_per_step": v["d2h"]} for k, v in res.items()},
+            "host_threads_per_rank": r["threads"] * 2,
+            "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; host expansion by two workers of the "
+                    "library's persistent thread pool, sized to this rank's share of the cores" % r["chunk"]}
 
 
 _JSON_FD = None
@@ -448,10 +597,16 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--debug-flags", type=int, default=0, help="kernel timing experiments (results invalid when non-zero)")
     ap.add_argument("--phases", action="store_true", help="also report the fused kernel's per-phase cycle shares")
+    ap.add_argument("--config", default=None, choices=sorted(PRESETS), help="preset of BASELINE.json: c2 (default workload), c3, c5")
+    ap.add_argument("--slices", type=int, default=0, help="4: MV3D height slices + intensity ON (extension E, generic path)")
+    ap.add_argument("--shuffle", action="store_true", help="sweeps in random point order instead of firing order")
+    ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained run reported beside the burst (0: off)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the short runs of the other configs (C3, C4, C5, ...)")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "ours" else a.warmup
-    sens = {"hdl32": 65536, "hdl64": 120000, "vls128": 249984}
-    a.n_pts = sens[a.sensor]
+    if a.config:
+        a.sensor, a.bev_res, a.sweeps = PRESETS[a.config]
+    a.n_pts = SENS[a.sensor]
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -212,12 +212,18 @@ SFPE_API int sfpe_roll_width(sfpe_ctx* ctx, const void* d_in, void* d_out, int64
  *                         the image's dtype); *d_flag (device int32, zeroed by the caller) is set to 1
  *                         if a value is not in the table.  d_bev 16-byte, d_codes 4-byte aligned;
  *   sfpe_bev_unpack_host  h_out[i] = (dtype) h_lut65[min(h_codes[i], 64)] on n_threads host threads
- *                         (<= 0: all cores), non-temporal stores.  Needs no context and no GPU. */
+ *                         (<= 0: all cores), non-temporal stores.  Needs no context and no GPU;
+ *   sfpe_bev_unpack_rgb_host  the picture the reference's BEV entry returns (uint8 [cell][3],
+ *                         birds_eye_view_generator.py:48-54): h_out[3i..3i+2] = h_rgb65[3*min(code,64)..], the
+ *                         colours of the 65 density values (sfpe_colormap of the table: parity unpinned).
+ * Host threads come from one persistent pool inside the library (grown on demand, shared by concurrent calls). */
 SFPE_API int sfpe_density_lut(sfpe_ctx* ctx, double* h_lut65);
 SFPE_API int sfpe_bev_pack_u8(sfpe_ctx* ctx, const void* d_bev, int32_t dtype, int64_t n_cells, uint8_t* d_codes,
                      int32_t* d_flag, void* stream);
 SFPE_API int sfpe_bev_unpack_host(const uint8_t* h_codes, int64_t n_cells, const double* h_lut65, void* h_out,
                          int32_t dtype, int32_t n_threads);
+SFPE_API int sfpe_bev_unpack_rgb_host(const uint8_t* h_codes, int64_t n_cells, const uint8_t* h_rgb65, uint8_t* h_out,
+                             int32_t n_threads);
 
 /* Back-projection of cluster centroids (train/predict.py:230-293, back_project_2D_2_3D).  Per item i:
  * if the pixel under the centroid is not valid (distance > 0 and height > min_height) and the box

@@ -79,6 +79,7 @@ SIGNATURES = {
     "sfpe_density_lut": (C.c_int, [C.c_void_p, C.c_void_p]),
     "sfpe_bev_pack_u8": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "sfpe_bev_unpack_host": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
+    "sfpe_bev_unpack_rgb_host": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32]),
     "sfpe_back_project": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32,
                                     C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
                                     C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -512,6 +512,14 @@ extern "C" int sfpe_bev_unpack_host(const uint8_t* h_codes, int64_t n_cells, con
   return SFPE_OK;
 }
 
+extern "C" int sfpe_bev_unpack_rgb_host(const uint8_t* h_codes, int64_t n_cells, const uint8_t* h_rgb65, uint8_t* h_out,
+                                        int32_t n_threads) {
+  if (n_cells < 0) return SFPE_ERR_INVALID_ARG;
+  if (n_cells > 0 && (!h_codes || !h_rgb65 || !h_out)) return SFPE_ERR_INVALID_ARG;
+  bev_unpack_rgb_host(h_codes, n_cells, h_rgb65, h_out, n_threads);
+  return SFPE_OK;
+}
+
 extern "C" int sfpe_back_project(sfpe_ctx* c, double* d_centroids, double* d_bboxes, int64_t n, const void* d_distance,
                                  const void* d_height, int32_t dtype, int64_t frame_stride, int32_t pix_stride,
                                  int32_t height, int32_t width, double min_height, double x_min, double res_rad,

@@ -101,6 +101,7 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
 cudaError_t launch_bev_pack_u8(const void* bev, int dtype, long long n, const double* lut, unsigned char* codes, int* bad,
                                int sm_count, cudaStream_t st, long long* launches);
 void bev_unpack_host(const unsigned char* codes, long long n, const double* lut65, void* out, int dtype, int n_threads);
+void bev_unpack_rgb_host(const unsigned char* codes, long long n, const unsigned char* rgb65, unsigned char* out, int n_threads);
 
 cudaError_t launch_selftest_fastpath(const DevGrid& g, const float* pts, long long n, unsigned long long* d_out4,
                                      cudaStream_t st, long long* launches);

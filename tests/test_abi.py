@@ -103,3 +103,40 @@ def test_bev_unpack_host_is_a_table_lookup(dtype):
             assert (buf[:3] == -7).all() and (buf[3 + n:] == -7).all()
     with pytest.raises(ValueError):
         proj.unpack_bev_host(np.zeros(4, np.uint8), lut[:10])
+
+
+def test_bev_unpack_rgb_host_is_a_table_lookup():
+    """Host half of the reference-typed BEV result (uint8 picture, birds_eye_view_generator.py:48-54; needs
+    no GPU): out[3i..3i+2] = rgb65[min(code[i], 64)], any alignment and length, neighbours untouched, several
+    calls at once on the library's persistent thread pool."""
+    import ctypes as C
+    import threading
+    lib = load_sub("_lib").load()
+    rng = np.random.default_rng(6)
+    tab = rng.integers(0, 256, (65, 3)).astype(np.uint8)
+
+    def one(n, off, threads):
+        codes = (rng.integers(0, 200, n) * (rng.random(n) < 0.05)).astype(np.uint8)
+        buf = np.full(3 * n + 64, 7, np.uint8)
+        out = buf[off:off + 3 * n]
+        rc = lib.sfpe_bev_unpack_rgb_host(codes.ctypes.data_as(C.c_void_p), n, tab.ctypes.data_as(C.c_void_p),
+                                          out.ctypes.data_as(C.c_void_p), threads)
+        assert rc == 0
+        assert np.array_equal(out, tab[np.minimum(codes, 64)].reshape(-1))
+        assert (buf[:off] == 7).all() and (buf[off + 3 * n:] == 7).all()
+
+    for n in [0, 1, 15, 16, 17, 1000, 300007]:
+        for off in (0, 1, 5):
+            one(n, off, 4)
+    errs = []
+
+    def many():
+        try:
+            for _ in range(20):
+                one(200000, 3, 3)
+        except Exception as e:     # pragma: no cover
+            errs.append(e)
+    th = [threading.Thread(target=many) for _ in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs

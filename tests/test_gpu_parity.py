@@ -587,6 +587,93 @@ def test_host_batch_pipeline_matches_device_batch(pkg, synth, transport):
     pr.close()
 
 
+def test_two_devices_in_one_process(pkg, synth):
+    """One sfpe_ctx per device, driven from two threads of ONE process (one host thread per
+    device): the fused kernel's opt-in to 227 KB of dynamic shared memory is a per-device attribute."""
+    import threading
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    sweeps = [synth.make_sweep("hdl32", seed=9900 + i) for i in range(6)]
+    allp = np.concatenate(sweeps)
+    res, err = {}, []
+
+    def work(dev):
+        try:
+            pr = pkg.LidarProjector(device=dev, path=2)
+            d = torch.from_numpy(allp).to(torch.device("cuda", dev))
+            with torch.cuda.device(dev):
+                out = pr.project(d, n_frames=len(sweeps), uniform_n=65536, winner=True)
+                torch.cuda.synchronize(dev)
+            assert pr.last_path == "fused"
+            res[dev] = {k: v.cpu().numpy() for k, v in out.items() if hasattr(v, "cpu")}
+            pr.close()
+        except Exception as e:      # surfaced in the main thread
+            err.append((dev, repr(e)))
+
+    th = [threading.Thread(target=work, args=(d,)) for d in (0, 1)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not err, err
+    for dev in (0, 1):
+        for f in (0, 5):
+            _check_frame(res[dev], f, sweeps[f])
+
+
+@pytest.mark.parametrize("transport", ["dense", "u8"])
+def test_host_batch_pipeline_back_to_back_runs(pkg, synth, transport):
+    """Two DIFFERENT batches issued back to back without a synchronize in between (what bench.py's e2e loop
+    does): the device slots are reused across run() calls, so the second run's uploads and kernels must
+    wait for the first run's kernels and downloads.  Each run has its own host outputs; both must be right."""
+    import torch
+    n_frames, n = 9, 65536
+    pins, refs = [], []
+    pr = pkg.LidarProjector(device=0, bev_res=(0.2, 0.2))
+    for b in range(3):
+        host = np.concatenate([synth.make_sweep("hdl32", seed=900 + 20 * b + i, shuffle=(i % 2 == b % 2)) for i in range(n_frames)])
+        pins.append(torch.from_numpy(host).pin_memory())
+        r = pr.alloc_outputs(n_frames)
+        pr.project(pins[-1].cuda(), n_frames=n_frames, uniform_n=n, out=r)
+        refs.append({k: r[k].cpu().numpy() for k in ("range", "bev", "status")})
+    hb = pkg.HostBatchPipeline(pr, n_frames, n, chunk=2, bev_transport=transport)
+    outs = [hb.host_outputs(), hb.alloc_host_outputs(), hb.alloc_host_outputs()]
+    for rep in range(3):                      # several rounds: any missing dependency gets its chance
+        for b in range(3):
+            hb.run(pins[b], out=outs[b])
+        hb.synchronize()
+        for b in range(3):
+            assert np.array_equal(outs[b]["range"].numpy(), refs[b]["range"]), (rep, b)
+            assert np.array_equal(outs[b]["bev"].numpy(), refs[b]["bev"]), (rep, b)
+            assert np.array_equal(outs[b]["status"].numpy(), refs[b]["status"]), (rep, b)
+    hb.close()
+    pr.close()
+
+
+@pytest.mark.parametrize("cmap", ["gray", "jet"])
+def test_host_batch_pipeline_rgb_is_the_reference_result_type(pkg, synth, cmap):
+    """bev_transport="rgb": the host receives what the reference's generate_birds_eye_view returns -- the
+    uint8 (nb, nb, 3) picture -- equal to the colormap stage applied to the float density image (the
+    drop-in's own path), and the (32,1801,3) float32 range tensor; no float BEV image on the host."""
+    import torch
+    n_frames, n = 5, 65536
+    host = np.concatenate([synth.make_sweep("hdl32", seed=950 + i) for i in range(n_frames)])
+    pin = torch.from_numpy(host).pin_memory()
+    pr = pkg.LidarProjector(device=0, bev_res=(0.2, 0.2))
+    ref = pr.alloc_outputs(n_frames)
+    pr.project(pin.cuda(), n_frames=n_frames, uniform_n=n, out=ref)
+    hb = pkg.HostBatchPipeline(pr, n_frames, n, chunk=2, bev_transport="rgb", cmap=cmap)
+    assert hb.h_bev is None and hb.h_bev_rgb.shape == (n_frames, pr.nbx, pr.nby, 3)
+    hb.run(pin)
+    hb.synchronize()
+    colormap = load_pkg().colormap
+    want = colormap.device_rgb(pr, ref["bev"], cmap, 0, 1500 * 0.2).cpu().numpy()
+    assert np.array_equal(hb.h_bev_rgb.numpy(), want)
+    assert np.array_equal(hb.h_range.numpy(), ref["range"].cpu().numpy())
+    assert hb.d2h_bytes == n_frames * (32 * 1801 * 3 * 4 + pr.nbx * pr.nby + 4)
+    hb.close()
+    pr.close()
+
+
 @pytest.mark.parametrize("cmap", ["gray", "jet"])
 def test_generate_birds_eye_view_single_device_pass(pkg, synth, cmap):
     """generate_birds_eye_view (birds_eye_view_generator.py:41-54) keeps the float image on the device;
