@@ -29,7 +29,19 @@
 // per ~4 cycles whatever its size, so the phases are tuned for few, full requests, and the
 // BEV image's 45 k lines per sweep are placed where the other phases issue the fewest.
 // HBM traffic: points read once (+ the winner gather), range written once, BEV written once.
+#include <stdio.h>
+
 #include "sfpe_internal.h"
+
+// -DSFPE_CHECKED builds: every index the kernel computes for a write into shared or global scratch is
+// checked against its buffer and traps on a violation (compute-sanitizer is not available on the GPU
+// pool; tools/checked_run.sh runs the fused-path tests on such a build).  No code in normal builds.
+#ifdef SFPE_CHECKED
+#define CHK(cond) do { if (!(cond)) { printf("SFPE_CHECKED failed: %s (line %d, block %d thread %d)\n", #cond, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define CHK(cond) do { } while (0)
+#endif
+
 
 namespace sfpe {
 
@@ -93,7 +105,7 @@ __device__ __forceinline__ void note_collision(uint2* __restrict__ cq, unsigned*
 
 // the same for the four points of a point-pass step: one reservation per thread
 __device__ __forceinline__ void note_collisions4(uint2* __restrict__ cq, unsigned* misc, const int (&cell)[4],
-                                                 const unsigned (&key)[4], const unsigned (&old)[4]) {
+                                                 const unsigned (&key)[4], const unsigned (&old)[4], unsigned cap) {
   unsigned nrec = 0u, hit = 0u;
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
@@ -102,6 +114,7 @@ __device__ __forceinline__ void note_collisions4(uint2* __restrict__ cq, unsigne
   }
   if (hit) {
     unsigned pos = atomicAdd(&misc[7], nrec);
+    CHK(pos + nrec <= cap);
 #pragma unroll
     for (int u = 0; u < 4; ++u)
       if (hit & (1u << u)) {
@@ -147,6 +160,7 @@ constexpr unsigned ENTRY_CELL = 0x3FFFFFFFu;
 __device__ __forceinline__ unsigned tile_count_issue(unsigned* tile, unsigned char* lf, unsigned e, unsigned tlo, unsigned T) {
   const unsigned r = (e & ENTRY_CELL) - tlo;
   if (r >= T) return 0u;
+  CHK(T <= (1u << 17));
   lf[r >> 5] = 1;
   const unsigned sh = (r & 3u) * 8u;
   const unsigned ob = (atomicAdd(tile + (r >> 2), ((e >> 30) + 1u) << sh) >> sh) & 0xFFu;
@@ -235,7 +249,7 @@ struct FusedArgs {
   FrameSet fs;
   unsigned* entries;   // [grid][n_buckets][per_cta] BEV entries (output cell + head) by tile bucket
   unsigned* queue;     // [grid][per_cta] deferred point indices
-  uint2* cqueue;       // [grid][6*per_cta] collision records (cell | bucket << 16, point index)
+  uint2* cqueue;       // [grid][6*per_cta] collision records (range-scan cell, point index)
   long long per_cta;
   const double* lut64;
   float* range; int range_layout; int* winner;
@@ -553,13 +567,16 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
         unsigned pos = atomicAdd(&misc[0], (unsigned)defer[0] + (unsigned)defer[1] + (unsigned)defer[2] + (unsigned)defer[3]);
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (defer[u]) my_queue[pos++] = (unsigned)(i0 + u * fstride);
+          if (defer[u]) { CHK(pos < per_cta32); my_queue[pos++] = (unsigned)(i0 + u * fstride); }
       }
       // the four shared-memory atomics of the range scan go out back to back; their results are
       // looked at after the BEV append (whose warp-wide steps they overlap)
       unsigned old[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) old[u] = (cell[u] >= 0 && !DBG(32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
+      for (int u = 0; u < 4; ++u) {
+        CHK(cell[u] < hw);
+        old[u] = (cell[u] >= 0 && !DBG(32)) ? atomicMin(keys + cell[u], key[u]) : KEY32_EMPTY;
+      }
       // BEV entries.  Neighbouring points of the thread in the same cell become one run (the count
       // - 1 rides in the two top bits of the entry).  Each run is appended to the bucket of its tile
       // with one shared-memory atomic per (warp, bucket): lanes with the same bucket elect a leader
@@ -578,10 +595,13 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           unsigned slot = 0u;
           if (lane == leader && bb[u] != NO_BUCKET) slot = atomicAdd(&bcnt[bb[u]], (unsigned)__popc(m));
           slot = __shfl_sync(0xFFFFFFFFu, slot, leader) + (unsigned)__popc(m & lane_lt);
-          if (bb[u] != NO_BUCKET) st_u32_hint(my_buckets + ((unsigned)bb[u] * per_cta32 + slot), be[u] | (cnt[u] << 30), keep);
+          if (bb[u] != NO_BUCKET) {
+            CHK(bb[u] < a.n_buckets && slot < per_cta32 && (be[u] >> a.tile_log2) < (unsigned)a.n_buckets * a.tiles_per_bucket);
+            st_u32_hint(my_buckets + ((unsigned)bb[u] * per_cta32 + slot), be[u] | (cnt[u] << 30), keep);
+          }
         }
       }
-      note_collisions4(my_cq, misc, cell, key, old);
+      note_collisions4(my_cq, misc, cell, key, old, 6u * per_cta32);
     };
     {
       float4 va[4], vb[4];
@@ -613,7 +633,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           if (bx >= 0 && by >= 0) {
             const unsigned e = cells_m1 - ((unsigned)bx * (unsigned)g.nby + (unsigned)by) + head;
             const int bk = (int)(e >> bucket_shift);
-            st_u32_hint(my_buckets + ((unsigned)bk * per_cta32 + atomicAdd(&bcnt[bk], 1u)), e, keep);
+            const unsigned slot = atomicAdd(&bcnt[bk], 1u);
+            CHK(bk < a.n_buckets && slot < per_cta32);
+            st_u32_hint(my_buckets + ((unsigned)bk * per_cta32 + slot), e, keep);
           }
         }
         if (g.enable_range) {
@@ -626,6 +648,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             atomicAdd(&misc[2], 1u);
           } else {
             const int cell = row * g.W + col;
+            CHK(cell >= 0 && cell < hw);
             const unsigned key = (quant_rho(rho) << IDX_BITS32) | i;
             note_collision(my_cq, misc, cell, key, atomicMin(keys + cell, key));
           }
@@ -961,6 +984,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             }
             // parked: four rows per word
             const unsigned hi = __shfl_down_sync(0xFFFFFFFFu, b16, 1);
+            CHK(r >= rhi || (((size_t)t * rpt + r) >> 2) < (size_t)(a.rows_cap >> 2));
             if ((lane & 1) == 0 && r < rhi) bm_k[((size_t)t * rpt + r) >> 2] = b16 | (hi << 16);
             const unsigned cnt = (unsigned)__popc(b16);
             unsigned inc = cnt;                     // inclusive prefix of the line counts over the lanes
@@ -977,6 +1001,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             while (b16) {
               const unsigned b = (unsigned)__ffs(b16) - 1u;
               b16 &= b16 - 1u;
+              CHK(off < (unsigned)(T >> 5));
               wl[off++] = (unsigned short)(base + b);
             }
           }
@@ -988,6 +1013,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           for (unsigned j = (unsigned)(tid >> 2); j < wn; j += CT / 4) {
             const unsigned li = wl[j];
             const int r = (int)(li >> 3), sct = (int)((li & 7u) << 2) + (lane & 3);
+            CHK(r < rpt && (size_t)(t * rpt + r) < (size_t)a.rows_cap);
             const uint2 w = tile2[r * 32 + sct];
             tile2[r * 32 + sct] = make_uint2(0u, 0u);
             float4 v0, v1;

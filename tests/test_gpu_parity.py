@@ -587,6 +587,36 @@ def test_host_batch_pipeline_matches_device_batch(pkg, synth, transport):
     pr.close()
 
 
+def test_fused_is_repeatable(pkg, synth):
+    """The fused kernel's warps talk through flags in shared memory (claims, parked tiles, pacing window) and
+    share scratch lists filled through atomics: ten launches over the same batch must give the same bits
+    (winners are decided by (range, index), never by arrival order), also while another stream keeps the
+    GPU busy."""
+    import torch
+    sweeps = [synth.make_sweep(("hdl32", "hdl64")[i % 2], seed=9800 + i, shuffle=(i % 5 == 0)) for i in range(160)]
+    n = [len(s) for s in sweeps]
+    offs = torch.from_numpy(np.concatenate([[0], np.cumsum(n)]).astype(np.int64)).cuda()
+    d = torch.from_numpy(np.concatenate(sweeps)).cuda()
+    pr = pkg.LidarProjector(device=0, path=2, firing_stride=32)
+    first = None
+    side = torch.cuda.Stream()
+    junk = torch.empty(64 << 20, dtype=torch.float32, device="cuda")
+    for rep in range(10):
+        if rep % 2:
+            with torch.cuda.stream(side):
+                for _ in range(20):
+                    junk.mul_(1.0001)
+        out = pr.project(d, n_frames=len(sweeps), frame_offsets=offs, max_n=max(n), winner=True)
+        torch.cuda.synchronize()
+        got = {k: out[k].clone() for k in ("range", "winner", "bev", "status", "dropped")}
+        if first is None:
+            first = got
+        else:
+            for k in got:
+                assert torch.equal(got[k], first[k]), (rep, k)
+    pr.close()
+
+
 def test_two_devices_in_one_process(pkg, synth):
     """One sfpe_ctx per device, driven from two threads of ONE process (one host thread per
     device): the fused kernel's opt-in to 227 KB of dynamic shared memory is a per-device attribute."""
