@@ -21,10 +21,11 @@ def to_rgb_bytes(img, cmap, vmin=None, vmax=None):
     pr = _session.projector(enable_bev=False)
     out = np.empty(a.shape + (3,), dtype=np.uint8)
     auto = vmin is None or vmax is None
-    rc = pr.lib.sfpe_colormap_host(
-        pr._ctx, a.ctypes.data_as(C.c_void_p), _lib.SFPE_F32 if a.dtype == np.float32 else _lib.SFPE_F64,
-        a.size, CMAPS[cmap], int(auto), 0.0 if auto else float(vmin), 0.0 if auto else float(vmax),
-        out.ctypes.data_as(C.c_void_p))
+    with pr._host_lock:
+        rc = pr.lib.sfpe_colormap_host(
+            pr._ctx, a.ctypes.data_as(C.c_void_p), _lib.SFPE_F32 if a.dtype == np.float32 else _lib.SFPE_F64,
+            a.size, CMAPS[cmap], int(auto), 0.0 if auto else float(vmin), 0.0 if auto else float(vmax),
+            out.ctypes.data_as(C.c_void_p))
     _lib.check(rc, pr._ctx)
     return out
 

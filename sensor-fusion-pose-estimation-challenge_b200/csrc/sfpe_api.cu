@@ -24,7 +24,7 @@ struct sfpe_ctx {
   // staging for sfpe_project_sweep_host
   void* st_points; size_t st_points_cap;
   void* st_range; void* st_bev; int* st_winner; int* st_status;  // status[0], dropped[1]
-  unsigned long long* d_mm;  // colormap autoscale {min,max}
+  unsigned long long* d_mm;  // [0..1] colormap autoscale {min,max}, [2..5] fast-path self-test maxima
   void* st_img; size_t st_img_cap; void* st_rgb; size_t st_rgb_cap;
   void* fused_buf; size_t fused_cap;  // entries + deferred queue of the fused path
   long long* d_prof; int prof_grid;   // phase profile of the fused kernel (sfpe_phase_profile)
@@ -192,7 +192,7 @@ extern "C" int sfpe_create(int device, const sfpe_params* p, sfpe_ctx** out) {
   CKC(cudaMalloc(&c->d_lut, 65 * sizeof(double)));
   c->scratch.lut = c->d_lut;
   CKC(cudaMalloc(&c->st_status, 2 * sizeof(int)));
-  CKC(cudaMalloc(&c->d_mm, 2 * sizeof(unsigned long long)));
+  CKC(cudaMalloc(&c->d_mm, 6 * sizeof(unsigned long long)));
   if (status == SFPE_OK) {
     CKC(launch_fill_scratch(g, c->scratch, c->chunk, c->stream, &c->launches));
     CKC(launch_density_lut(c->d_lut, c->stream, &c->launches));
@@ -443,13 +443,10 @@ extern "C" int sfpe_phase_cycles(sfpe_ctx* c, int64_t* out8) {
 extern "C" int sfpe_selftest_fastpath(sfpe_ctx* c, const float* d_xyzi, int64_t n, double* out4) {
   if (!c || !out4 || n < 0 || (n > 0 && !d_xyzi) || ((uintptr_t)d_xyzi & 15)) return SFPE_ERR_INVALID_ARG;
   CK(c, cudaSetDevice(c->device));
-  unsigned long long* d = nullptr;
-  CK(c, cudaMalloc((void**)&d, 4 * sizeof(unsigned long long)));
-  cudaError_t e = launch_selftest_fastpath(c->grid, d_xyzi, n, d, c->stream, &c->launches);
-  if (e == cudaSuccess) e = cudaMemcpyAsync(out4, d, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-  cudaFree(d);
-  CK(c, e);
+  unsigned long long* d = c->d_mm + 2;   // scratch owned by the ctx (no allocation per call)
+  CK(c, launch_selftest_fastpath(c->grid, d_xyzi, n, d, c->stream, &c->launches));
+  CK(c, cudaMemcpyAsync(out4, d, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  CK(c, cudaStreamSynchronize(c->stream));
   return SFPE_OK;
 }
 

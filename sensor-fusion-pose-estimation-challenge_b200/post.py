@@ -135,7 +135,7 @@ def back_project_device(centroids, bboxes, range_scan=None, distance=None, heigh
     for t, cols in ((centroids, 2), (bboxes, 4)):
         if t.dtype != torch.float64 or tuple(t.shape) != (B, cols) or not t.is_contiguous() or t.device != dev:
             raise ValueError("centroids (B,2) and bboxes (B,4) must be contiguous float64 tensors on %s" % dev)
-    xyz = torch.empty((B, 4), dtype=torch.float64, device=dev)
+    xyz = torch.zeros((B, 4), dtype=torch.float64, device=dev)    # status-3 items keep zeros (the kernel writes nothing)
     status = torch.empty((B,), dtype=torch.int32, device=dev)
     pr = _projector(dev)
     rc = pr.lib.sfpe_back_project(
@@ -289,11 +289,12 @@ def locate_obstacles(prediction, range_scan, stream=None):
     obs = find_obstacle_device(prediction, H, W, stream=stream, posbits=posbits)
     centroids = obs[:, 1:3].to(torch.float64).contiguous()
     bboxes = obs[:, 3:7].to(torch.float64).contiguous()
-    xyz, _ = back_project_device(centroids, bboxes, range_scan=range_scan, stream=stream)
+    xyz, bp_status = back_project_device(centroids, bboxes, range_scan=range_scan, stream=stream)
     pred, _, n_boxes = find_bbox_3d_device(prediction, obs[:, 3:7].contiguous(), xyz[:, :3].contiguous(),
                                            range_scan=range_scan, stream=stream, posbits=posbits)
     _release_on(stream, posbits)
-    found = (obs[:, 0] != 0) & ~((xyz[:, 0] == 0) & (xyz[:, 1] == 0)) & (n_boxes > 0)      # :349, :358, :137
+    # status 3: the cluster's box or centroid lies outside the image (the reference would index out of range)
+    found = (obs[:, 0] != 0) & (bp_status != 3) & ~((xyz[:, 0] == 0) & (xyz[:, 1] == 0)) & (n_boxes > 0)      # :349, :358, :137
     return torch.where(found[:, None], pred, torch.zeros_like(pred)), found
 
 

@@ -4,6 +4,12 @@ Same names, arguments, return layout and error behaviour as the reference; the w
 done on the GPU by libsfpe.so (one H2D copy of the sweep, kernels, one D2H copy of the
 three float64 (32,1801) images).  The bag-walking CLI of the reference module is out of
 scope.
+
+dtype contract: the reference's callers hand over float64 arrays (np.array(list(read_points(msg))));
+every cell decision here is made in float64 on the values given.  A float32 array is widened first,
+i.e. it gives the images of the float64 array of the same values (numpy would evaluate a float32
+array in float32 arithmetic, which no caller of the reference does).  The functions may be called
+from several threads (one projector per parameter set, calls serialised per projector).
 """
 import numpy as np
 

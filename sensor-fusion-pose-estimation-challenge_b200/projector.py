@@ -63,6 +63,10 @@ class LidarProjector:
         ctx = C.c_void_p()
         _lib.check(self.lib.sfpe_create(self.device, C.byref(p), C.byref(ctx)))
         self._ctx = ctx
+        # the *_host entries of one ctx share its stream and staging buffers: one caller at a time
+        # (the drop-in free functions share one projector per parameter set, see _session.py)
+        import threading
+        self._host_lock = threading.Lock()
 
     # ------------------------------------------------------------------ lifecycle
     def close(self):
@@ -252,7 +256,11 @@ class LidarProjector:
     def project_sweep_host(self, points, columns=(0, 1, 2, 3), range_dtype=np.float64, range_layout="chw",
                            bev_dtype=np.float64, want_range=True, want_bev=True, want_winner=False):
         """points: C-contiguous numpy (N, >=4) float32/float64 on the host.  Returns
-        (range, winner, bev, status, dropped) as numpy arrays (None where not wanted)."""
+        (range, winner, bev, status, dropped) as numpy arrays (None where not wanted).
+        dtype contract: every decision is evaluated in float64 on the VALUES given, as the reference
+        does on the float64 array its callers build (np.array(list(read_points(msg))),
+        lidar_predict.py:64-65); a float32 array is widened first and gives the same images as the
+        float64 array of the same values (numpy itself would evaluate a float32 array in float32)."""
         a = np.asarray(points)
         if a.ndim != 2 or a.shape[1] <= max(columns):
             raise ValueError("points must be (N, >=4)")
@@ -277,10 +285,11 @@ class LidarProjector:
             bev = np.empty((self.nbx, self.nby), dtype=_NP_OF[bdt])
         st, dr = C.c_int32(0), C.c_int32(0)
         vp = lambda x: x.ctypes.data_as(C.c_void_p) if x is not None else None
-        rc = self.lib.sfpe_project_sweep_host(
-            self._ctx, vp(a) if len(a) else None, C.byref(d), len(a), vp(rng), rdt,
-            _lib.RANGE_CHW if range_layout == "chw" else _lib.RANGE_HWC, vp(win), vp(bev), bdt,
-            C.byref(st), C.byref(dr))
+        with self._host_lock:
+            rc = self.lib.sfpe_project_sweep_host(
+                self._ctx, vp(a) if len(a) else None, C.byref(d), len(a), vp(rng), rdt,
+                _lib.RANGE_CHW if range_layout == "chw" else _lib.RANGE_HWC, vp(win), vp(bev), bdt,
+                C.byref(st), C.byref(dr))
         _lib.check(rc, self._ctx)
         return rng, win, bev, st.value, dr.value
 

@@ -204,6 +204,34 @@ def test_float64_inputs_not_float32_representable(pkg):
     _check_density(d, lo.bev_density(P, (0.2, 0.2), 120))
 
 
+def test_dropin_float32_input_is_float64_semantics_and_thread_safe(pkg, synth):
+    """dtype contract of the drop-ins: a float32 array gives the images of the float64 array of the same
+    values (the reference's callers always build float64 arrays).  And the free functions may be called
+    from several threads at once (they share one projector; the reference's functions are pure)."""
+    import threading
+    sweeps = [synth.make_sweep("hdl32", seed=8200 + i, n_az=700) for i in range(4)]
+    want = [pkg.generate_lidar_2d_front_view(_P(s)) for s in sweeps]
+    dens = [pkg.birds_eye_view_density(_P(s), (0.2, 0.2), 120) for s in sweeps]
+    a32 = pkg.generate_lidar_2d_front_view(sweeps[0])                  # float32 (N,4) as it is
+    for k in ("distance_float", "height_float", "intensity_float"):
+        assert a32[k].dtype == np.float64 and np.array_equal(a32[k], want[0][k])
+    errs = []
+
+    def work(i):
+        try:
+            for _ in range(10):
+                got = pkg.generate_lidar_2d_front_view(_P(sweeps[i]))
+                for k in ("distance_float", "height_float", "intensity_float"):
+                    assert np.array_equal(got[k], want[i][k]), (i, k)
+                assert np.array_equal(pkg.birds_eye_view_density(_P(sweeps[i]), (0.2, 0.2), 120), dens[i]), i
+        except Exception as e:
+            errs.append(repr(e))
+    th = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+
+
 def test_order_invariance_and_conservation(pkg, synth):
     """Size-independent properties at the bench's sweep size: shuffling the points changes
     nothing but the winner indices; every in-range point is counted exactly once."""
