@@ -42,7 +42,8 @@ def generate_birds_eye_view(arrPoints, t, res, max_range=120, cmap='gray'):
     import torch
     if points.dtype not in (np.float32, np.float64):
         points = points.astype(np.float64)
-    d_pts = torch.from_numpy(np.ascontiguousarray(points)).to(torch.device("cuda", pr.device))
-    out = pr.project(d_pts, n_frames=1, uniform_n=len(points), bev_dtype="f64")
-    rgb = colormap.device_rgb(pr, out["bev"][0], cmap, 0, vmax)
-    return rgb.cpu().numpy()
+    with pr._host_lock:       # the shared projector's scratch: one caller at a time
+        d_pts = torch.from_numpy(np.ascontiguousarray(points)).to(torch.device("cuda", pr.device))
+        out = pr.project(d_pts, n_frames=1, uniform_n=len(points), bev_dtype="f64")
+        rgb = colormap.device_rgb(pr, out["bev"][0], cmap, 0, vmax)
+        return rgb.cpu().numpy()
