@@ -241,18 +241,21 @@ __device__ __forceinline__ float floor_small(float t, int& fi) {
 __device__ __forceinline__ float rint_small(float t) { return __fadd_rn(t, 12582912.0f) - 12582912.0f; }
 
 // Returns true when (row, col) = trunc(yi), trunc(xi) is PROVEN equal to the fp64 result and
-// inside the image; false -> the caller must use range_cell_f64.  Cell boundaries under
-// truncation toward zero are the NON-ZERO integers.  Written so that NaN anywhere gives false.
+// inside the image; false -> the caller must use range_cell_f64.  A coordinate is proven when it
+// lies at least EPS away from both neighbouring integers (the fraction is within 0.5 - EPS of 0.5);
+// under truncation toward zero the integer 0 is not a cell boundary, but the few points within EPS
+// of it are simply left to the fp64 path as well.  Accepted coordinates are > -0.5, where truncation
+// toward zero = max(floor, 0).  The range test (-0.5, W) is |xi - c| < h with c = W/2 - 0.25,
+// h = W/2 + 0.25 (both exact in fp32, and rounding of the difference is monotone, so a coordinate
+// outside the interval can never pass).  Written so that NaN anywhere gives false.
 __device__ __forceinline__ bool range_cell_decide(const DevGrid& g, float xi, float yi, float q, int& row, int& col) {
-  const float cx = rint_small(xi), cy = rint_small(yi);
-  const bool near_x = fabsf(xi - cx) <= EPS_COL && cx != 0.0f;
-  const bool near_y = fabsf(yi - cy) <= EPS_ROW && cy != 0.0f;
-  // accepted coordinates are > -0.5, where truncation toward zero = max(floor, 0)
   int fx, fy;
-  floor_small(xi, fx); floor_small(yi, fy);
+  const float frx = xi - floor_small(xi, fx), fry = yi - floor_small(yi, fy);
   col = max(fx, 0);
   row = max(fy, 0);
-  return !near_x && !near_y && fabsf(q) <= MAX_SIN_EL && xi > -0.5f && yi > -0.5f && xi < (float)g.W && yi < (float)g.H;
+  const float hW = 0.5f * (float)g.W, hH = 0.5f * (float)g.H;
+  return fabsf(frx - 0.5f) < 0.5f - EPS_COL && fabsf(fry - 0.5f) < 0.5f - EPS_ROW && fabsf(q) <= MAX_SIN_EL &&
+         fabsf(xi - (hW - 0.25f)) < hW + 0.25f && fabsf(yi - (hH - 0.25f)) < hH + 0.25f;
 }
 
 // fp32 BEV bin candidate with guard band; -2 = undecided (caller uses bev_bin_f64, which also

@@ -499,10 +499,16 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
 
     auto load4 = [&](float4 (&v)[4], int q) {
       const int i0 = step_base(q) + lane;
+      const float4* const p0 = fp + i0;
+      if (i0 - lane + 3 * fstride + 32 <= n32) {   // the whole step lies inside the frame (warp-uniform): no bounds checks
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int i = i0 + u * fstride;
-        v[u] = i < n32 ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int u = 0; u < 4; ++u) v[u] = __ldg(p0 + u * fstride);
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = i0 + u * fstride;
+          v[u] = i < n32 ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
     };
     auto rasterise4 = [&](const float4 (&v)[4], const int q) {
@@ -528,11 +534,14 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           int ibx, iby;
           const float flx = floor_small(tx, ibx), fly = floor_small(ty, iby);
           const float frx = tx - flx, fry = ty - fly;
-          const float nbxf = (float)g.nbx, nbyf = (float)g.nby;
-          const bool inx = frx > g.bev_eps_x_f && frx < 1.0f - g.bev_eps_x_f && tx > 0.0f && tx < nbxf;   // proven bin
-          const bool iny = fry > g.bev_eps_y_f && fry < 1.0f - g.bev_eps_y_f && ty > 0.0f && ty < nbyf;
-          const bool outx = tx < -1.0f || tx > nbxf + 1.0f;                                               // proven outside
-          const bool outy = ty < -1.0f || ty > nbyf + 1.0f;
+          // proven bin: the fraction at least eps away from both edges and 0 < t < nb, as |t - nb/2| < nb/2
+          // (nb/2 is exact and the rounding of the difference is monotone); proven outside: |t - nb/2| > nb/2 + 1
+          const float hx = 0.5f * (float)g.nbx, hy = 0.5f * (float)g.nby;
+          const float dx = fabsf(tx - hx), dy = fabsf(ty - hy);
+          const bool inx = fabsf(frx - 0.5f) < 0.5f - g.bev_eps_x_f && dx < hx;
+          const bool iny = fabsf(fry - 0.5f) < 0.5f - g.bev_eps_y_f && dy < hy;
+          const bool outx = dx > hx + 1.0f;
+          const bool outy = dy > hy + 1.0f;
           // NaN: neither in nor out -> undecided -> fp64 (which drops it, like histogram2d)
           undecided = !(outx || outy) && !(inx && iny);
           const unsigned e = cells_m1 - ((unsigned)ibx * (unsigned)g.nby + (unsigned)iby) + head;

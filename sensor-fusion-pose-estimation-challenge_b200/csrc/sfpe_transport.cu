@@ -180,9 +180,18 @@ void unpack_threads(const uint8_t* codes, long long n, const double* lut65, T* o
   });
 }
 
-// codes -> RGB bytes through a 64-colour table (3 bytes per cell).  16 cells (48 bytes) per step; an
-// all-empty group -- the rule: > 95 % of a BEV image -- is three non-temporal 16-byte stores of the
-// background colour.
+// codes -> RGB bytes through a 64-colour table (3 bytes per cell).  16 cells (48 bytes) per step, built
+// in six 64-bit registers: they start as the background colour and the few non-empty cells of a group
+// (> 95 % of a BEV image is empty) are patched in with shifts and masks -- no byte stores that a wide
+// load would have to wait for -- then go out as three non-temporal 16-byte stores.
+static inline void put24(uint64_t (&w)[6], int k, uint64_t rgb) {     // bytes 3k..3k+2 of the 48-byte group
+  const int bit = 24 * k, q = bit >> 6, sh = bit & 63;
+  w[q] = (w[q] & ~(0xFFFFFFull << sh)) | (rgb << sh);
+  if (sh > 40) {                                                      // straddles two words
+    const int r = 64 - sh;
+    w[q + 1] = (w[q + 1] & ~(0xFFFFFFull >> r)) | (rgb >> r);
+  }
+}
 void unpack_rgb_slice(const uint8_t* codes, long long n, const uint8_t* table /* [256][4] */, uint8_t* out) {
   long long i = 0;
 #if defined(__SSE2__)
@@ -191,25 +200,29 @@ void unpack_rgb_slice(const uint8_t* codes, long long n, const uint8_t* table /*
     out[3 * i] = c[0]; out[3 * i + 1] = c[1]; out[3 * i + 2] = c[2];
     ++i;
   }
-  alignas(16) uint8_t bg[48];
-  for (int k = 0; k < 16; ++k) { bg[3 * k] = table[0]; bg[3 * k + 1] = table[1]; bg[3 * k + 2] = table[2]; }
-  const __m128i b0 = _mm_load_si128(reinterpret_cast<const __m128i*>(bg)), b1 = _mm_load_si128(reinterpret_cast<const __m128i*>(bg + 16)),
-                b2 = _mm_load_si128(reinterpret_cast<const __m128i*>(bg + 32));
+  uint32_t rgb[256];
+  for (int k = 0; k < 256; ++k) rgb[k] = (uint32_t)table[4 * k] | ((uint32_t)table[4 * k + 1] << 8) | ((uint32_t)table[4 * k + 2] << 16);
+  uint64_t bg[6] = {0, 0, 0, 0, 0, 0};
+  for (int k = 0; k < 16; ++k) put24(bg, k, rgb[0]);
+  const __m128i b0 = _mm_set_epi64x((long long)bg[1], (long long)bg[0]), b1 = _mm_set_epi64x((long long)bg[3], (long long)bg[2]),
+                b2 = _mm_set_epi64x((long long)bg[5], (long long)bg[4]);
   const __m128i zero = _mm_setzero_si128();
   for (; i + 16 <= n; i += 16) {
     const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i*>(codes + i));
     __m128i* o = reinterpret_cast<__m128i*>(out + 3 * i);
-    if (_mm_movemask_epi8(_mm_cmpeq_epi8(c, zero)) == 0xFFFF) {
+    unsigned nz = 0xFFFFu & ~(unsigned)_mm_movemask_epi8(_mm_cmpeq_epi8(c, zero));
+    if (nz == 0u) {
       _mm_stream_si128(o, b0); _mm_stream_si128(o + 1, b1); _mm_stream_si128(o + 2, b2);
     } else {
-      alignas(16) uint8_t t[48];
-      for (int k = 0; k < 16; ++k) {
-        const uint8_t* q = table + 4 * codes[i + k];
-        t[3 * k] = q[0]; t[3 * k + 1] = q[1]; t[3 * k + 2] = q[2];
+      uint64_t w[6] = {bg[0], bg[1], bg[2], bg[3], bg[4], bg[5]};
+      while (nz) {
+        const int k = __builtin_ctz(nz);
+        nz &= nz - 1u;
+        put24(w, k, rgb[codes[i + k]]);
       }
-      _mm_stream_si128(o, _mm_load_si128(reinterpret_cast<const __m128i*>(t)));
-      _mm_stream_si128(o + 1, _mm_load_si128(reinterpret_cast<const __m128i*>(t + 16)));
-      _mm_stream_si128(o + 2, _mm_load_si128(reinterpret_cast<const __m128i*>(t + 32)));
+      _mm_stream_si128(o, _mm_set_epi64x((long long)w[1], (long long)w[0]));
+      _mm_stream_si128(o + 1, _mm_set_epi64x((long long)w[3], (long long)w[2]));
+      _mm_stream_si128(o + 2, _mm_set_epi64x((long long)w[5], (long long)w[4]));
     }
   }
   _mm_sfence();
