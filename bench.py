@@ -512,6 +512,22 @@ def verify_frames(a, pkg, path_timed, d_pts, out, local, rank, k=8):
     return len(frames)
 
 
+def host_traffic(a, pr, res):
+    """What the host's DRAM carries per sweep for each result form (DMA reads of the points, DMA writes of the
+    copied-back bytes, the expansion's reads and writes) and the GB/s that makes at the measured rate: the ceiling
+    of e2e is this traffic -- all ranks of a box share one host -- not the GPUs or (except "dense") the PCIe link."""
+    cells, rng_b, pts_b = pr.nbx * pr.nby, 32 * 1801 * 3 * 4, a.n_pts * 16
+    out = {}
+    for k, v in res.items():
+        d2h = rng_b + (cells * 4 if k == "dense" else cells)
+        exp_r = 0 if k == "dense" else cells
+        exp_w = 0 if k == "dense" else cells * (3 if k == "rgb" else 4)
+        per = pts_b + d2h + exp_r + exp_w
+        out[k] = {"bytes_per_sweep": per, "dma": pts_b + d2h, "expansion": exp_r + exp_w,
+                  "GBps_at_measured_rate": round(per * v["value"] / 1e9, 1), "pcie_d2h_GBps": round(d2h * v["value"] / 1e9, 1)}
+    return out
+
+
 def run_e2e(a, pkg, pr, pin_in, dev, world):
     """Host pinned in -> H2D -> kernels -> D2H of every output image, pipelined over chunks on 3 streams.
     Three result forms are timed: "dense" (float32 BEV over PCIe), "u8" (one byte per BEV cell over PCIe,
@@ -554,6 +570,7 @@ def run_e2e(a, pkg, pr, pin_in, dev, world):
             "by_result": {k: {"sweeps_per_s": round(v["value"], 1), "host_result": host_result[k],
                               "d2h_bytes_per_step": v["d2h"]} for k, v in res.items()},
             "host_threads_per_rank": r["threads"] * 2,
+            "host_memory_traffic": host_traffic(a, pr, res),
             "note": "pinned host in/out, %d-sweep chunks pipelined on 3 streams; host expansion by two workers of the "
                     "library's persistent thread pool, sized to this rank's share of the cores" % r["chunk"]}
 
