@@ -53,7 +53,8 @@ typedef enum {
   SFPE_ERR_INVALID_ARG = -1,
   SFPE_ERR_CUDA = -2,
   SFPE_ERR_UNSUPPORTED = -3,
-  SFPE_ERR_NOMEM = -4
+  SFPE_ERR_NOMEM = -4,
+  SFPE_ERR_TOO_LARGE = -5 /* sfpe_range_scan_static: H*W beyond SFPE_STATIC_MAX_CELLS */
 } sfpe_status;
 
 /* element types of point fields and float outputs */
@@ -152,6 +153,24 @@ SFPE_API const char* sfpe_last_error(const sfpe_ctx* ctx); /* text of the last C
 SFPE_API int sfpe_project_batch(sfpe_ctx* ctx, const sfpe_points* pts, const int64_t* d_frame_offsets,
                        int64_t uniform_n, int64_t max_n, int32_t n_frames,
                        const sfpe_outputs* out, void* stream);
+
+/* The range scan of sfpe_project_batch WITHOUT any allocation, for callers that may not call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in
+ * the reference.  Needs no ctx: `device` and the
+ * parameter block are passed per call (enable_bev / n_slices are ignored: range scan only; the BEV
+ * members of `out` must be NULL).  Same point layouts, frame offsets, outputs (range, range_winner,
+ * status, dropped) and results as sfpe_project_batch; it runs the generic kernels with their
+ * winner-key scratch in a static device array of SFPE_STATIC_MAX_CELLS 64-bit keys (2 MiB, held by
+ * every GPU that loads the library until the process exits).  A grid with H*W beyond that is refused
+ * with SFPE_ERR_TOO_LARGE (the default 32 x 1801 grid uses 22 % of it; frames are processed
+ * floor(SFPE_STATIC_MAX_CELLS / (H*W)) at a time).  Calls no cudaMalloc / cudaFree / allocating
+ * routine; the first call per device looks the array's address up (cudaGetSymbolAddress), so make
+ * one call before capturing a graph.  Leaves `device` current.  Asynchronous on `stream`.  All calls
+ * on a device share the array: calls that overlap on the GPU (two streams, two threads) race. */
+#define SFPE_STATIC_MAX_CELLS (1 << 18)
+SFPE_API int sfpe_range_scan_static(int device, const sfpe_params* p, const sfpe_points* pts,
+                           const int64_t* d_frame_offsets, int64_t uniform_n, int64_t max_n,
+                           int32_t n_frames, const sfpe_outputs* out, void* stream);
 
 /* One sweep, HOST in / HOST out (pinned or pageable): H2D, kernels, D2H, synchronised.
  * host_points has n points in the layout `layout` describes (layout->data ignored).

@@ -14,6 +14,8 @@ SFPE_F32, SFPE_F64 = 0, 1
 RANGE_CHW, RANGE_HWC = 0, 1
 FRAME_ROW_OOB, FRAME_COL_OOB, FRAME_NAN = 1, 2, 4
 MAX_SLICES = 8
+STATIC_MAX_CELLS = 1 << 18   # sfpe_range_scan_static: largest H*W
+ERR_TOO_LARGE = -5
 ABI_VERSION = 1
 
 
@@ -63,6 +65,8 @@ SIGNATURES = {
     "sfpe_last_error": (C.c_char_p, [C.c_void_p]),
     "sfpe_project_batch": (C.c_int, [C.c_void_p, C.POINTER(Points), C.c_void_p, C.c_int64, C.c_int64,
                                      C.c_int32, C.POINTER(Outputs), C.c_void_p]),
+    "sfpe_range_scan_static": (C.c_int, [C.c_int, C.POINTER(Params), C.POINTER(Points), C.c_void_p, C.c_int64,
+                                         C.c_int64, C.c_int32, C.POINTER(Outputs), C.c_void_p]),
     "sfpe_project_sweep_host": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Points), C.c_int64, C.c_void_p,
                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int32,
                                           C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),

@@ -48,6 +48,7 @@ extern "C" const char* sfpe_strerror(int s) {
     case SFPE_ERR_CUDA: return "CUDA error (see sfpe_last_error)";
     case SFPE_ERR_UNSUPPORTED: return "unsupported configuration";
     case SFPE_ERR_NOMEM: return "out of memory";
+    case SFPE_ERR_TOO_LARGE: return "grid larger than the static scratch (H*W > SFPE_STATIC_MAX_CELLS)";
     default: return "unknown status";
   }
 }
@@ -127,6 +128,10 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
     g->bev_eps_y_f = 3.0f * (nextafterf((float)g->ney, INFINITY) - (float)g->ney);
   }
   return SFPE_OK;
+}
+
+namespace sfpe {
+int derive_grid_for(const sfpe_params* p, DevGrid* g) { return derive_grid(p, g); }  // for sfpe_static.cu
 }
 
 extern "C" int sfpe_grid_dims(const sfpe_params* p, int32_t* H, int32_t* W, int32_t* nbx, int32_t* nby) {

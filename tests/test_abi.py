@@ -64,6 +64,27 @@ def test_invalid_params_rejected():
     assert lib_mod.load().sfpe_strerror(-3) == b"unsupported configuration"
 
 
+def test_static_entry_validates_before_touching_cuda():
+    """sfpe_range_scan_static: size and argument checks are host arithmetic (no GPU needed)."""
+    import ctypes as C
+    lib_mod = load_sub("_lib")
+    lib = lib_mod.load()
+    desc, o = lib_mod.Points(), lib_mod.Outputs()
+    desc.stride_bytes, desc.off_y, desc.off_z, desc.off_i = 16, 4, 8, 12
+    call = lambda p, n_frames: lib.sfpe_range_scan_static(0, C.byref(p), C.byref(desc), None, 0, 0, n_frames,
+                                                          C.byref(o), None)
+    p = lib_mod.default_params()
+    assert call(p, 0) == 0                                    # nothing to do
+    p.res_h_deg = 0.02
+    assert call(p, 1) == lib_mod.ERR_TOO_LARGE
+    assert b"SFPE_STATIC_MAX_CELLS" in lib.sfpe_strerror(lib_mod.ERR_TOO_LARGE)
+    p = lib_mod.default_params()
+    p.res_v_deg = 0.0
+    assert call(p, 1) == -1
+    src = open(os.path.join(ROOT, "include", "sfpe.h")).read()
+    assert "#define SFPE_STATIC_MAX_CELLS (1 << 18)" in src and lib_mod.STATIC_MAX_CELLS == 1 << 18
+
+
 def test_no_cpu_fallback_without_gpu():
     import torch
     if torch.cuda.is_available():
