@@ -325,6 +325,15 @@ def run_ours(a):
 
     # ---- the timed launch is checked: K random frames of the batch are rasterised again by the generic
     # (global-atomics, fp64) path and must equal the slices of the timed output bit for bit (every rank)
+    # (one more launch of the same step into NaN-filled outputs first: a frame whose lines were not written
+    # in that launch cannot hide behind the values an earlier launch left in the buffer)
+    if not a.debug_flags:
+        for key in ("range", "bev"):
+            out[key].fill_(float("nan"))
+        step()
+        torch.cuda.synchronize()
+        if bool(torch.isnan(out["bev"]).any()) or bool(torch.isnan(out["range"]).any()):
+            raise RuntimeError("bench: the step left parts of its outputs unwritten")
     verified = verify_frames(a, pkg, path_timed, d_pts, out, local, rank)
     if world > 1:
         v = torch.tensor([verified], device=dev, dtype=torch.int64)
@@ -421,10 +430,29 @@ def measure_config(pkg, local, sensor, bev_res, sweeps, steps=4, warmup=3, shuff
     bytes_sweep = algorithmic_bytes(n_pts, pr.nbx, pr.nby, c_bev)
     peak, _ = measured_peak()
     ok = int((out["status"] != 0).sum().item()) == 0
+    # checked like the main line: one more launch into NaN-filled outputs, every byte written, and random frames
+    # equal to the generic path's rasterisation of the same points
+    verified = 0
+    if pr.last_path == "fused":
+        for key in ("range", "bev"):
+            out[key].fill_(float("nan"))
+        pr.project(d_pts, n_frames=sweeps, uniform_n=n_pts, out=out)
+        torch.cuda.synchronize()
+        if bool(torch.isnan(out["bev"]).any()) or bool(torch.isnan(out["range"]).any()):
+            raise RuntimeError("bench: %s left parts of its outputs unwritten" % sensor)
+        chk = pkg.LidarProjector(device=local, bev_res=(bev_res, bev_res), path=1)
+        for f in sorted(int(x) for x in np.random.default_rng(99).choice(sweeps, size=min(4, sweeps), replace=False)):
+            o = chk.project(d_pts[f * n_pts:(f + 1) * n_pts], n_frames=1, uniform_n=n_pts)
+            torch.cuda.synchronize()
+            for key in ("range", "bev", "status", "dropped"):
+                if not torch.equal(o[key][0], out[key][f]):
+                    raise RuntimeError("bench: %s frame %d differs from the generic path in %r" % (sensor, f, key))
+            verified += 1
+        chk.close()
     res = {"sweeps_per_s": sweeps / (ms * 1e-3), "points_per_s": sweeps * n_pts / (ms * 1e-3), "sweeps": sweeps,
            "points_per_sweep": n_pts, "bev_res_m": bev_res, "path": pr.last_path, "launch_ms": ms,
            "algorithmic_bytes_per_sweep": bytes_sweep, "frac": sweeps * bytes_sweep / (ms * 1e-3) / 1e9 / peak,
-           "all_frames_ok": ok}
+           "all_frames_ok": ok, "verified_frames": verified}
     pr.close()
     del out, d_pts
     torch.cuda.empty_cache()

@@ -118,6 +118,11 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
   g->inv_res_v_f = (float)(1.0 / g->res_rad_v);
   g->neg_x_min_f = (float)(-g->x_min);
   g->neg_y_min_f = (float)(-g->y_min);
+  {
+    const float hW = 0.5f * (float)g->W, hH = 0.5f * (float)g->H;   // exact
+    g->rc_cx_f = hW - 0.25f; g->rc_hx_f = hW + 0.25f;
+    g->rc_cy_f = hH - 0.25f; g->rc_hy_f = hH + 0.25f;
+  }
   if (g->enable_bev) {
     // t = (v - start)/delta = v*inv + c0; guard = 3 ulp32 at the largest bin coordinate
     g->bev_inv_x_f = (float)g->bev_inv_delta_x;
@@ -126,6 +131,9 @@ static int derive_grid(const sfpe_params* p, DevGrid* g) {
     g->bev_c0_y_f = (float)(-g->bev_start * g->bev_inv_delta_y);
     g->bev_eps_x_f = 3.0f * (nextafterf((float)g->nex, INFINITY) - (float)g->nex);
     g->bev_eps_y_f = 3.0f * (nextafterf((float)g->ney, INFINITY) - (float)g->ney);
+    g->bev_hx_f = 0.5f * (float)g->nbx; g->bev_hy_f = 0.5f * (float)g->nby;
+    g->bev_hx1_f = g->bev_hx_f + 1.0f;  g->bev_hy1_f = g->bev_hy_f + 1.0f;
+    g->bev_fe_x_f = 0.5f - g->bev_eps_x_f; g->bev_fe_y_f = 0.5f - g->bev_eps_y_f;
   }
   return SFPE_OK;
 }

@@ -38,6 +38,11 @@ struct DevGrid {
   // fp32 BEV candidate: t = v * bev_inv_f + bev_c0_f (in bins), guard band bev_eps_f bins
   float bev_inv_x_f, bev_c0_x_f, bev_eps_x_f;
   float bev_inv_y_f, bev_c0_y_f, bev_eps_y_f;
+  // derived once on the host so that the point pass takes them as constant-bank operands (the same
+  // fp32 operations the kernel used to repeat per point): range tests |t - c| < h of range_cell_decide,
+  // BEV half extents nb/2, nb/2 + 1 and the fraction bound 0.5 - eps
+  float rc_cx_f, rc_hx_f, rc_cy_f, rc_hy_f;
+  float bev_hx_f, bev_hy_f, bev_hx1_f, bev_hy1_f, bev_fe_x_f, bev_fe_y_f;
 };
 
 struct PointSrc {
@@ -253,9 +258,11 @@ __device__ __forceinline__ bool range_cell_decide(const DevGrid& g, float xi, fl
   const float frx = xi - floor_small(xi, fx), fry = yi - floor_small(yi, fy);
   col = max(fx, 0);
   row = max(fy, 0);
-  const float hW = 0.5f * (float)g.W, hH = 0.5f * (float)g.H;
-  return fabsf(frx - 0.5f) < 0.5f - EPS_COL && fabsf(fry - 0.5f) < 0.5f - EPS_ROW && fabsf(q) <= MAX_SIN_EL &&
-         fabsf(xi - (hW - 0.25f)) < hW + 0.25f && fabsf(yi - (hH - 0.25f)) < hH + 0.25f;
+  // c = g.rc_c?_f, h = g.rc_h?_f (host: derive_grid); no short circuit: five compares, no branch
+  const bool in_fx = fabsf(frx - 0.5f) < 0.5f - EPS_COL, in_fy = fabsf(fry - 0.5f) < 0.5f - EPS_ROW;
+  const bool in_q = fabsf(q) <= MAX_SIN_EL;
+  const bool in_x = fabsf(xi - g.rc_cx_f) < g.rc_hx_f, in_y = fabsf(yi - g.rc_cy_f) < g.rc_hy_f;
+  return in_fx & in_fy & in_q & in_x & in_y;
 }
 
 // fp32 BEV bin candidate with guard band; -2 = undecided (caller uses bev_bin_f64, which also

@@ -391,7 +391,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   //       [6] frames claimed so far, [7] collision records, [9] claim broadcast, [10] parked sectors of the
   //       frame in S2, [11] store-warp pacing window, [12..15] claim ring: frame + 1 (~0: no more frames),
   //       [16..39] phase cycles, [40..103] entries per bucket, [104..107] ring: misc[5] when the frame was
-  //       claimed, [108..109] block cursor of the frame being written (by frame parity)
+  //       claimed, [108..109] block cursor of the frame being written (by frame parity), [110] frames whose
+  //       cursor has been reset (S2 begun)
   unsigned* const misc = smem + main_words + 136;
   const int tid = threadIdx.x;
   const int hw = g.H * g.W;
@@ -416,6 +417,9 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       while ((int)(ld_acquire_smem(&misc[6]) - (k + 1u)) < 0) __nanosleep(1000);
       const unsigned c = *reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]);
       if (c == ~0u) return;
+      // the frame's block cursor still holds the count of frame k - 2 until the compute warps reset it at the
+      // start of the frame's S2 (misc[110]); a claim before that would read "no blocks left" and skip the frame
+      while ((int)(ld_acquire_smem(&misc[110]) - (k + 1u)) < 0) __nanosleep(1000);
       const BevJob j = make_bev_job(a, cells, (int)c - 1, k, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k & 3u)]));
       bev_write_frame(j, &misc[108 + (k & 1u)], misc, sl, true);
       __syncwarp();
@@ -536,12 +540,11 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           const float frx = tx - flx, fry = ty - fly;
           // proven bin: the fraction at least eps away from both edges and 0 < t < nb, as |t - nb/2| < nb/2
           // (nb/2 is exact and the rounding of the difference is monotone); proven outside: |t - nb/2| > nb/2 + 1
-          const float hx = 0.5f * (float)g.nbx, hy = 0.5f * (float)g.nby;
-          const float dx = fabsf(tx - hx), dy = fabsf(ty - hy);
-          const bool inx = fabsf(frx - 0.5f) < 0.5f - g.bev_eps_x_f && dx < hx;
-          const bool iny = fabsf(fry - 0.5f) < 0.5f - g.bev_eps_y_f && dy < hy;
-          const bool outx = dx > hx + 1.0f;
-          const bool outy = dy > hy + 1.0f;
+          const float dx = fabsf(tx - g.bev_hx_f), dy = fabsf(ty - g.bev_hy_f);
+          const bool inx = (fabsf(frx - 0.5f) < g.bev_fe_x_f) & (dx < g.bev_hx_f);
+          const bool iny = (fabsf(fry - 0.5f) < g.bev_fe_y_f) & (dy < g.bev_hy_f);
+          const bool outx = dx > g.bev_hx1_f;
+          const bool outy = dy > g.bev_hy1_f;
           // NaN: neither in nor out -> undecided -> fp64 (which drops it, like histogram2d)
           undecided = !(outx || outy) && !(inx && iny);
           const unsigned e = cells_m1 - ((unsigned)ibx * (unsigned)g.nby + (unsigned)iby) + head;
@@ -886,6 +889,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           misc[11] = 1u;
         }
         misc[108 + par] = 0u;
+        st_release_smem(&misc[110], frames_done + 1u);   // the store warp may claim blocks of this frame
       }
       PROF_STAMP(8);
       for (int w = tid; w < ((tw + lbw) >> 2); w += CT) reinterpret_cast<uint4*>(tile)[w] = make_uint4(0u, 0u, 0u, 0u);   // tw, lbw: multiples of 4

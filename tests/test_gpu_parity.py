@@ -118,7 +118,12 @@ def _check_frame(res, f, pts32, bev_res=(0.2, 0.2), layout="hwc", strict_ok=True
 
 def _check_density(got, dens64):
     if got.dtype == np.float32:
-        assert np.array_equal(got, dens64.astype(np.float32))
+        want = dens64.astype(np.float32)
+        if not np.array_equal(got, want):
+            bad = np.argwhere(got != want)
+            raise AssertionError("BEV density: %d cells differ, rows %d..%d; first (row, col, got, want): %s" % (
+                len(bad), bad[:, 0].min(), bad[:, 0].max(),
+                [(int(r), int(c), float(got[r, c]), float(want[r, c])) for r, c in bad[:8]]))
     else:
         assert np.array_equal(got == 0, dens64 == 0)
         np.testing.assert_allclose(got, dens64, rtol=DENSITY_RTOL, atol=0)
@@ -517,6 +522,39 @@ def test_fused_rewrites_every_bev_byte(pkg, synth):
         assert torch.isnan(buf[:256 + shift]).all() and torch.isnan(buf[256 + shift + len(sweeps) * cells:]).all()
         for f in (0, 4, 8):
             _check_density(out["bev"][f].cpu().numpy(), lo.bev_density(_P(sweeps[f]), (0.2, 0.2), 120))
+    pr.close()
+
+
+@pytest.mark.parametrize("sensor,frames_per_sm", [("vls128", 6), ("hdl64", 7)])
+def test_fused_store_warp_never_skips_a_frame(pkg, synth, sensor, frames_per_sm):
+    """Six or seven sweeps per CTA with a long point pass and the small (0.2 m) image: the store warp is
+    done with a frame's zero lines long before the compute warps reach the next frame's BEV phase.  It
+    must then wait for that frame's block cursor to be reset (a stale cursor reads "no blocks left" and
+    the frame's zero lines would never be written; with fewer than five frames per CTA the CTA's last two
+    frames, written by all warps at the end, hide it).  Outputs start as NaN; every frame is compared on
+    the device with the generic path's result for the same sweep."""
+    import torch
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    distinct = 8
+    n_frames = (sms * frames_per_sm + distinct - 1) // distinct * distinct
+    sweeps = [synth.make_sweep(sensor, seed=7000 + i, near_heavy=(sensor == "vls128")) for i in range(distinct)]
+    n_pts = len(sweeps[0])
+    base = torch.from_numpy(np.concatenate(sweeps)).cuda()
+    ref = _device_batch(pkg, base, distinct, n_pts, 1, (0.2, 0.2))
+    d = base.repeat(n_frames // distinct, 1)
+    pr = pkg.LidarProjector(device=0, path=2, firing_stride=synth.SENSORS[sensor][0])
+    for rep in range(2):
+        out = pr.alloc_outputs(n_frames, winner=True)
+        out["bev"].fill_(float("nan"))
+        out["range"].fill_(float("nan"))
+        pr.project(d, n_frames=n_frames, uniform_n=n_pts, out=out)
+        torch.cuda.synchronize()
+        assert pr.last_path == "fused"
+        for k in ("bev", "range", "winner"):
+            got = out[k].view((n_frames // distinct, distinct) + tuple(out[k].shape[1:]))
+            same = (got == ref[k][None]).flatten(2).all(dim=2)
+            assert bool(same.all()), "%s: frames %s differ" % (k, torch.nonzero(~same.flatten())[:16].flatten().tolist())
+        del out
     pr.close()
 
 
