@@ -360,7 +360,7 @@ def run_ours(a):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(path_timed, a.sweeps), "peak_source": peak_src,
                          "algorithmic_bytes_per_sweep": bytes_sweep, "launch_ms": med_ms,
-                         "kernel": "fused k_fused_sweep (one launch per step)" if path_timed == "fused"
+                         "kernel": "fused k_fused_sweep (one launch per step)" if path_timed.startswith("fused")
                          else "generic path: whole step (k_project + k_resolve_range + k_resolve_bev per chunk)"},
             "clocks": clocks,
         }
@@ -433,18 +433,20 @@ def measure_config(pkg, local, sensor, bev_res, sweeps, steps=4, warmup=3, shuff
     # checked like the main line: one more launch into NaN-filled outputs, every byte written, and random frames
     # equal to the generic path's rasterisation of the same points
     verified = 0
-    if pr.last_path == "fused":
-        for key in ("range", "bev"):
-            out[key].fill_(float("nan"))
+    if pr.last_path.startswith("fused"):
+        keys = ("range", "bev", "status", "dropped") + (("bev_height", "bev_intensity") if slice_edges is not None else ())
+        for key in keys:
+            if out[key].is_floating_point():
+                out[key].fill_(float("nan"))
         pr.project(d_pts, n_frames=sweeps, uniform_n=n_pts, out=out)
         torch.cuda.synchronize()
-        if bool(torch.isnan(out["bev"]).any()) or bool(torch.isnan(out["range"]).any()):
+        if any(bool(torch.isnan(out[key]).any()) for key in keys if out[key].is_floating_point()):
             raise RuntimeError("bench: %s left parts of its outputs unwritten" % sensor)
-        chk = pkg.LidarProjector(device=local, bev_res=(bev_res, bev_res), path=1)
+        chk = pkg.LidarProjector(device=local, bev_res=(bev_res, bev_res), path=1, slice_edges=slice_edges)
         for f in sorted(int(x) for x in np.random.default_rng(99).choice(sweeps, size=min(4, sweeps), replace=False)):
             o = chk.project(d_pts[f * n_pts:(f + 1) * n_pts], n_frames=1, uniform_n=n_pts)
             torch.cuda.synchronize()
-            for key in ("range", "bev", "status", "dropped"):
+            for key in keys:
                 if not torch.equal(o[key][0], out[key][f]):
                     raise RuntimeError("bench: %s frame %d differs from the generic path in %r" % (sensor, f, key))
             verified += 1
@@ -525,7 +527,7 @@ def verify_frames(a, pkg, path_timed, d_pts, out, local, rank, k=8):
     points (range tensor and BEV density, bit for bit); raises otherwise.  0 when the timed path was the
     generic one itself."""
     import torch
-    if path_timed != "fused" or a.debug_flags:
+    if not path_timed.startswith("fused") or a.debug_flags:
         return 0
     rng = np.random.default_rng(1234 + rank)
     frames = sorted(int(f) for f in rng.choice(a.sweeps, size=min(k, a.sweeps), replace=False))
@@ -643,7 +645,7 @@ def main():
     ap.add_argument("--debug-flags", type=int, default=0, help="kernel timing experiments (results invalid when non-zero)")
     ap.add_argument("--phases", action="store_true", help="also report the fused kernel's per-phase cycle shares")
     ap.add_argument("--config", default=None, choices=sorted(PRESETS), help="preset of BASELINE.json: c2 (default workload), c3, c5")
-    ap.add_argument("--slices", type=int, default=0, help="4: MV3D height slices + intensity ON (extension E, generic path)")
+    ap.add_argument("--slices", type=int, default=0, help="4: MV3D height slices + intensity ON (extension E: k_fused_sweep + the sfpe_ext.cu kernels)")
     ap.add_argument("--shuffle", action="store_true", help="sweeps in random point order instead of firing order")
     ap.add_argument("--sustain", type=float, default=2.0, help="seconds of the sustained run reported beside the burst (0: off)")
     ap.add_argument("--no-configs", action="store_true", help="skip the short runs of the other configs (C3, C4, C5, ...)")

@@ -294,7 +294,8 @@ SFPE_API int sfpe_find_obstacle(sfpe_ctx* ctx, const void* d_pred, int32_t pred_
 
 /* Kernels launched by this ctx since creation (bench.py's gpu_launches). */
 SFPE_API int64_t sfpe_launch_count(const sfpe_ctx* ctx);
-/* Name of the code path the last sfpe_project_batch took ("generic", "fused"). */
+/* Name of the code path the last sfpe_project_batch took ("generic", "fused", "fused+ext": the fused kernel
+ * followed by the height-slice / intensity kernels of the extension). */
 SFPE_API const char* sfpe_last_path(const sfpe_ctx* ctx);
 
 /* Profiling hook (no reference counterpart; the reference's analogue is the cProfile toggle at

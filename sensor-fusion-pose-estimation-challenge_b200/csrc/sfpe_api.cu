@@ -28,6 +28,7 @@ struct sfpe_ctx {
   void* st_img; size_t st_img_cap; void* st_rgb; size_t st_rgb_cap;
   void* fused_buf; size_t fused_cap;  // entries + deferred queue of the fused path
   long long* d_prof; int prof_grid;   // phase profile of the fused kernel (sfpe_phase_profile)
+  void* ext_buf; size_t ext_cap; size_t ext_top_bytes;   // extension E next to the fused kernel: top keys + per-point cells of a chunk
 };
 
 #define CK(ctx, call)                                                                   \
@@ -227,7 +228,7 @@ extern "C" void sfpe_destroy(sfpe_ctx* c) {
   cudaFree(c->scratch.keys); cudaFree(c->scratch.counts); cudaFree(c->scratch.top);
   cudaFree(c->scratch.slice_max); cudaFree(c->d_lut);
   cudaFree(c->st_points); cudaFree(c->st_range); cudaFree(c->st_bev); cudaFree(c->st_winner);
-  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb); cudaFree(c->fused_buf); cudaFree(c->d_prof);
+  cudaFree(c->st_status); cudaFree(c->d_mm); cudaFree(c->st_img); cudaFree(c->st_rgb); cudaFree(c->fused_buf); cudaFree(c->d_prof); cudaFree(c->ext_buf);
   if (c->stream) cudaStreamDestroy(c->stream);
   free(c);
 }
@@ -318,6 +319,35 @@ extern "C" int sfpe_project_batch(sfpe_ctx* c, const sfpe_points* pts, const int
     fx.prof = (c->d_prof && fx.grid <= c->prof_grid) ? c->d_prof : nullptr;
     CK(c, launch_fused(g, src, fs, c->scratch, out, fx, st, &c->launches));
     c->last_path = "fused";
+    if (g.n_slices && (out.bev_height || out.bev_intensity)) {
+      // extension E: dense fill of the planes + two passes over the points (sfpe_ext.cu), in chunks of
+      // frames whose top-key scratch stays within 256 MB
+      const size_t cells = (size_t)g.nbx * g.nby;
+      size_t xchunk = (256u << 20) / (cells * 8);
+      if (xchunk < 1) xchunk = 1;
+      if (xchunk > 64) xchunk = 64;
+      if (xchunk > (size_t)n_frames) xchunk = n_frames;
+      const size_t top_bytes = (xchunk * cells * 8 + 255) & ~(size_t)255;
+      const size_t need_bytes = top_bytes + xchunk * (size_t)(max_n > 0 ? max_n : 1) * 4;
+      if (c->ext_cap < need_bytes) {
+        const int xrc = grow(c, &c->ext_buf, &c->ext_cap, need_bytes);
+        if (xrc) return xrc;
+        CK(c, cudaMemsetAsync(c->ext_buf, 0, top_bytes, st));
+      } else if (c->ext_top_bytes != top_bytes) {
+        CK(c, cudaMemsetAsync(c->ext_buf, 0, c->ext_cap, st));   // other layout than the last call: all idle again
+      }
+      c->ext_top_bytes = top_bytes;
+      ExtScratch xs;
+      xs.top = (unsigned long long*)c->ext_buf;
+      xs.pcell = (int*)((char*)c->ext_buf + top_bytes);
+      xs.max_n = max_n > 0 ? max_n : 1;
+      for (int f0 = 0; f0 < n_frames; f0 += (int)xchunk) {
+        fs.frame0 = f0;
+        fs.n_frames = n_frames - f0 < (int)xchunk ? n_frames - f0 : (int)xchunk;
+        CK(c, launch_ext_chunk(g, src, fs, max_n, xs, out, st, &c->launches));
+      }
+      c->last_path = "fused+ext";
+    }
     return SFPE_OK;
   }
   if (want == 2) return SFPE_ERR_UNSUPPORTED;

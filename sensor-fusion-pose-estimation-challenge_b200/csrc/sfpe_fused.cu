@@ -1099,7 +1099,7 @@ FusedGeom fused_geometry(const DevGrid& g) {
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n) {
   const bool packed = src.dtype == 0 && src.stride == 16 && src.ox == 0 && src.oy == 4 && src.oz == 8 &&
                       src.oi == 12 && ((uintptr_t)src.data & 15) == 0;
-  if (!packed || g.use_extrinsic || g.n_slices || max_n > FUSED_MAX_N) return false;
+  if (!packed || g.use_extrinsic || max_n > FUSED_MAX_N) return false;   // (height slices: sfpe_ext.cu, after this kernel)
   if (g.enable_range && (out.range_dtype != 0 || g.H * g.W > main_words_max())) return false;
   if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts)) return false;
   if (g.enable_bev && (long long)g.nbx * g.nby > 0x3FF00000ll) return false;   // entries: 30-bit tile coordinate + 2-bit run length

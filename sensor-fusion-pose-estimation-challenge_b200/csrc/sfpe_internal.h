@@ -97,6 +97,15 @@ cudaError_t prepare_fused();   // per device: opt in to the large dynamic shared
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
                          const DevOut& out, const FusedScratch& fx, cudaStream_t st, long long* launches);
 
+// extension E next to the fused kernel (height-slice planes + intensity of the highest point) -- sfpe_ext.cu
+struct ExtScratch {
+  unsigned long long* top;   // [chunk][nbx*nby] key of the cell's highest point, 0 when idle (the winners reset it)
+  int* pcell;                // [chunk][max_n]   BEV cell of a point that takes part, -1 otherwise
+  long long max_n;
+};
+cudaError_t launch_ext_chunk(const DevGrid& g, const PointSrc& src, const FrameSet& fs, long long max_n,
+                             const ExtScratch& xs, const DevOut& out, cudaStream_t st, long long* launches);
+
 // sfpe_transport.cu: one-byte-per-cell transport of the BEV density image
 cudaError_t launch_bev_pack_u8(const void* bev, int dtype, long long n, const double* lut, unsigned char* codes, int* bad,
                                int sm_count, cudaStream_t st, long long* launches);
