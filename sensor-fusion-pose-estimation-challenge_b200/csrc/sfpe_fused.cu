@@ -124,11 +124,25 @@ __device__ __forceinline__ void note_collisions4(uint2* __restrict__ cq, unsigne
   }
 }
 
+// Rigid extrinsic (extension, default off; XF instantiation of the kernel only): exactly apply_extrinsic of
+// sfpe_common.cuh -- the affine map in fp64, left to right, not fused, rounded to float32 -- so that the
+// transformed cloud is again a float32 cloud and every fp32 decision and guard band applies to it unchanged.
+template <bool XF>
+__device__ __forceinline__ float4 xf_point(const DevGrid& g, float4 v) {
+  if (XF) {
+    Pt p; p.x = v.x; p.y = v.y; p.z = v.z; p.it = v.w;
+    apply_extrinsic(g, p);
+    v.x = (float)p.x; v.y = (float)p.y; v.z = (float)p.z;
+  }
+  return v;
+}
+
 // candidate (point idx, coordinates v) against the holder of *addr: `cur` is the key read
 // before and hv the coordinates of ITS point (both loaded by the caller, so that the loads of
 // several candidates are in flight together); reloaded only when the holder changes under us.
-__device__ __forceinline__ void settle_candidate(const float4* __restrict__ frame_pts, unsigned* addr, const float4 v,
-                                                 unsigned idx, unsigned cur, float4 hv) {
+template <bool XF>
+__device__ __forceinline__ void settle_candidate(const DevGrid& g, const float4* __restrict__ frame_pts, unsigned* addr,
+                                                 const float4 v, unsigned idx, unsigned cur, float4 hv) {
   const double rho = rho_of_f4(v);
   const unsigned my_key = (quant_rho(rho) << IDX_BITS32) | idx;
   for (;;) {
@@ -141,7 +155,7 @@ __device__ __forceinline__ void settle_candidate(const float4* __restrict__ fram
     const unsigned seen = atomicCAS(addr, cur, my_key);
     if (seen == cur) return;
     cur = seen;
-    hv = __ldg(frame_pts + (cur & IDX_MASK32));
+    hv = xf_point<XF>(g, __ldg(frame_pts + (cur & IDX_MASK32)));
   }
 }
 
@@ -313,6 +327,7 @@ __device__ __forceinline__ void lut8(const float* lut, const uint2 e, float4& v0
 // themselves or wait on loads, unpaced when they wait for the store warp.  (Faster inside the
 // window and every SM -- they run in step -- saturates HBM with zeros while the point loads
 // starve; measured optimum, profiles/README.md.)
+template <bool XF>   // one copy per kernel instantiation (a copy shared by two kernels was assembled wrongly: see __graft_entry__.check_sass)
 __device__ __noinline__ void bev_write_frame(const BevJob& job, unsigned* cursor, unsigned* misc, const int lane,
                                              const bool paced) {
   const BevJob j = job;   // in registers (the caller's copy lives in local memory)
@@ -380,6 +395,7 @@ __device__ __noinline__ void bev_write_frame(const BevJob& job, unsigned* cursor
     }                                                           \
   } while (0)
 
+template <bool XF>   // XF: apply the extrinsic to every point that is loaded
 __global__ void __launch_bounds__(FUSED_THREADS, 1)
 k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedArgs a, const int main_words) {
   extern __shared__ __align__(16) unsigned smem[];
@@ -421,7 +437,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       // start of the frame's S2 (misc[110]); a claim before that would read "no blocks left" and skip the frame
       while ((int)(ld_acquire_smem(&misc[110]) - (k + 1u)) < 0) __nanosleep(1000);
       const BevJob j = make_bev_job(a, cells, (int)c - 1, k, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k & 3u)]));
-      bev_write_frame(j, &misc[108 + (k & 1u)], misc, sl, true);
+      bev_write_frame<XF>(j, &misc[108 + (k & 1u)], misc, sl, true);
       __syncwarp();
       if (sl == 0) st_release_smem(&misc[4], k + 1u);   // the parked bitmaps of frame k may be overwritten
     }
@@ -530,7 +546,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       for (int u = 0; u < 4; ++u) {
         const int i = i0 + u * fstride;
         const bool valid = i < n32;
-        const float x = v[u].x, y = v[u].y, z = v[u].z;
+        const float4 w = xf_point<XF>(g, v[u]);
+        const float x = w.x, y = w.y, z = w.z;
         bool undecided = false;
         be[u] = 0u; bb[u] = NO_BUCKET; cell[u] = -1; key[u] = 0u;
         if (do_bev) {   // uniform
@@ -636,7 +653,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       const unsigned qn = misc[0];
       for (unsigned j = tid; j < qn; j += CT) {
         const unsigned i = my_queue[j];
-        const float4 v = __ldg(fp + i);
+        const float4 v = xf_point<XF>(g, __ldg(fp + i));
         if (do_bev) {
           const int bx = bev_bin_f64((double)v.x, g.bev_start, g.bev_delta_x, g.nex);
           const int by = bev_bin_f64((double)v.y, g.bev_start, g.bev_delta_y, g.ney);
@@ -689,8 +706,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             cur[u] = keys[en[u].x];
             if ((cur[u] & IDX_MASK32) == en[u].y) { act[u] = false; continue; }   // the holder itself has nothing to do
             if (DBG(512)) { pv[u] = make_float4(1.f, 2.f, 3.f, (float)en[u].y); hv[u] = make_float4(1.f, 2.f, 3.f, (float)cur[u]); continue; }
-            pv[u] = __ldg(fp + en[u].y);
-            hv[u] = __ldg(fp + (cur[u] & IDX_MASK32));
+            pv[u] = xf_point<XF>(g, __ldg(fp + en[u].y));
+            hv[u] = xf_point<XF>(g, __ldg(fp + (cur[u] & IDX_MASK32)));
           }
           if (DBG(256)) {
 #pragma unroll
@@ -700,7 +717,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           }
 #pragma unroll
           for (int u = 0; u < 4; ++u)
-            if (act[u]) settle_candidate(fp, keys + en[u].x, pv[u], en[u].y, cur[u], hv[u]);
+            if (act[u]) settle_candidate<XF>(g, fp, keys + en[u].x, pv[u], en[u].y, cur[u], hv[u]);
         }
       }
       compute_sync();
@@ -807,9 +824,10 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
             d[j] = 0.f; h[j] = height_bg; it[j] = 0.f; win[j] = -1;
             if (key[j] != KEY32_EMPTY) {
               win[j] = (int)(key[j] & IDX_MASK32);
-              const double x = v[j].x, y = v[j].y;
+              const float4 w = xf_point<XF>(g, v[j]);
+              const double x = w.x, y = w.y;
               d[j] = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
-              h[j] = v[j].z; it[j] = v[j].w;
+              h[j] = w.z; it[j] = w.w;
             }
           }
           if (DBG(2)) { if (d[0] + h[1] + it[2] + d[3] == 1.2345f) a.range[0] = 1.f; continue; }
@@ -844,7 +862,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           int win = -1;
           if (key != KEY32_EMPTY) {
             win = (int)(key & IDX_MASK32);
-            const float4 v = __ldg(fp + win);
+            const float4 v = xf_point<XF>(g, __ldg(fp + win));
             const double x = v.x, y = v.y;
             d = (float)__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)));
             h = v.z; it = v.w;
@@ -1060,7 +1078,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     for (unsigned k = frames_done >= 2u ? frames_done - 2u : 0u; k < frames_done; ++k) {
       const int fk = (int)*reinterpret_cast<volatile unsigned*>(&misc[12 + (k & 3u)]) - 1;
       const BevJob j = make_bev_job(a, cells, fk, k, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k & 3u)]));
-      bev_write_frame(j, &misc[108 + (k & 1u)], misc, lane, false);
+      bev_write_frame<XF>(j, &misc[108 + (k & 1u)], misc, lane, false);
     }
     PROF_STAMP(10);
   }
@@ -1099,7 +1117,7 @@ FusedGeom fused_geometry(const DevGrid& g) {
 bool fused_supported(const DevGrid& g, const PointSrc& src, const DevOut& out, long long max_n) {
   const bool packed = src.dtype == 0 && src.stride == 16 && src.ox == 0 && src.oy == 4 && src.oz == 8 &&
                       src.oi == 12 && ((uintptr_t)src.data & 15) == 0;
-  if (!packed || g.use_extrinsic || max_n > FUSED_MAX_N) return false;   // (height slices: sfpe_ext.cu, after this kernel)
+  if (!packed || max_n > FUSED_MAX_N) return false;   // (height slices: sfpe_ext.cu, after this kernel; extrinsic: the XF instantiation)
   if (g.enable_range && (out.range_dtype != 0 || g.H * g.W > main_words_max())) return false;
   if (g.enable_bev && (out.bev_dtype != 0 || out.bev_counts)) return false;
   if (g.enable_bev && (long long)g.nbx * g.nby > 0x3FF00000ll) return false;   // entries: 30-bit tile coordinate + 2-bit run length
@@ -1114,7 +1132,9 @@ int fused_grid(int device, int n_frames) {
 
 cudaError_t prepare_fused() {
   // per device (per primary context): called from sfpe_create after cudaSetDevice
-  return cudaFuncSetAttribute(k_fused_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  const cudaError_t e = cudaFuncSetAttribute(k_fused_sweep<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(k_fused_sweep<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
 }
 
 cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& fs, const Scratch& s,
@@ -1142,7 +1162,8 @@ cudaError_t launch_fused(const DevGrid& g, const PointSrc& src, const FrameSet& 
   a.prof = fx.prof;
   a.debug = fx.debug;
   const size_t smem = (size_t)(main_words + SMEM_MISC_WORDS) * 4;
-  k_fused_sweep<<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
+  if (g.use_extrinsic) k_fused_sweep<true><<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
+  else k_fused_sweep<false><<<fx.grid, FUSED_THREADS, smem, st>>>(g, a, main_words);
   ++*launches;
   return cudaGetLastError();
 }

@@ -420,7 +420,7 @@ def test_extension_height_slices_and_intensity(pkg, synth, with_extrinsic):
     out = pr.project(torch.from_numpy(np.concatenate(sweeps)).cuda(), n_frames=len(sweeps),
                      frame_offsets=torch.from_numpy(offs).cuda(), max_n=max(len(s) for s in sweeps))
     torch.cuda.synchronize()
-    assert pr.last_path == ("generic" if with_extrinsic else "fused+ext")
+    assert pr.last_path == "fused+ext"
     for f, s in enumerate(sweeps):
         P = _P(s)
         if with_extrinsic:   # the transformed cloud is again a float32 cloud (sfpe_common.cuh apply_extrinsic)
@@ -433,25 +433,29 @@ def test_extension_height_slices_and_intensity(pkg, synth, with_extrinsic):
     pr.close()
 
 
-def test_extension_next_to_the_fused_kernel_equals_generic(pkg, synth):
+@pytest.mark.parametrize("with_extrinsic", [False, True])
+def test_extension_next_to_the_fused_kernel_equals_generic(pkg, synth, with_extrinsic):
     """Extension E on the bench's shape (HDL-64E-shaped sweeps, 0.2 m, four slices): the fused kernel followed by
     the fill / project / finish kernels of sfpe_ext.cu gives the generic path's planes bit for bit, on
-    back-to-back calls with different batch sizes (the top-key scratch resets itself) and into NaN-filled outputs."""
+    back-to-back calls with different batch sizes (the top-key scratch resets itself) and into NaN-filled outputs.
+    With the rigid extrinsic the fused kernel's XF instantiation transforms every point it loads (fp64, rounded
+    to float32, as the generic path does): range scan, winners, density and planes all equal the generic path's."""
     import torch
     edges = [-2.0, -1.0, 0.0, 1.0, 3.0]
+    M = np.array([[0.999, -0.04, 0.01, 0.3], [0.04, 0.999, 0.0, -0.2], [-0.01, 0.0, 1.0, 0.15]]) if with_extrinsic else None
     sweeps = [synth.make_sweep("hdl64", seed=7300 + i, shuffle=(i % 5 == 2), dropout=0.1 * (i % 3)) for i in range(27)]
     sweeps[4] = sweeps[4][:0]
     top = sweeps[0][np.argsort(-sweeps[0][:, 2])[:200]].copy()   # ties on z: the lowest index wins
     top[:, 3] += 1.0
     sweeps[0] = np.concatenate([sweeps[0], top]).astype(np.float32)
-    fused = pkg.LidarProjector(device=0, slice_edges=edges)   # one ctx for all calls: its scratch is reused
+    fused = pkg.LidarProjector(device=0, slice_edges=edges, extrinsic=M)   # one ctx for all calls: its scratch is reused
     for n_frames in (27, 3, 27):
         part = sweeps[:n_frames]
         offs = torch.from_numpy(np.cumsum([0] + [len(s) for s in part]).astype(np.int64)).cuda()
         d = torch.from_numpy(np.concatenate(part)).cuda()
         res = {}
         for path in (0, 1):
-            pr = pkg.LidarProjector(device=0, slice_edges=edges, path=1) if path else fused
+            pr = pkg.LidarProjector(device=0, slice_edges=edges, extrinsic=M, path=1) if path else fused
             out = pr.alloc_outputs(n_frames, winner=True)
             for k in ("range", "bev", "bev_height", "bev_intensity"):
                 out[k].fill_(float("nan"))
@@ -465,6 +469,11 @@ def test_extension_next_to_the_fused_kernel_equals_generic(pkg, synth):
             assert torch.equal(res[0][k], res[1][k]), (n_frames, k)
     fused.close()
     P = _P(sweeps[0])
+    if with_extrinsic:
+        xyz = (M[:, 0] * P[:, 0:1] + M[:, 1] * P[:, 1:2]) + M[:, 2] * P[:, 2:3] + M[:, 3]
+        P[:, :3] = xyz.astype(np.float32).astype(np.float64)
+        o = lo.front_view(P, strict=False)
+        assert np.array_equal(res[0]["winner"][0].cpu().numpy(), o["winner"].astype(np.int32))
     h, it = lo.bev_height_intensity(P, (0.2, 0.2), 120, edges)
     assert np.array_equal(res[0]["bev_height"][0].cpu().numpy(), h.astype(np.float32))
     assert np.array_equal(res[0]["bev_intensity"][0].cpu().numpy(), it.astype(np.float32))
