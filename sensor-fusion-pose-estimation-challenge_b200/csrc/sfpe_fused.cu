@@ -448,7 +448,6 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
   unsigned* const bcnt = misc + 40;   // entries per bucket [MAX_BUCKETS]
   const int lane = tid & 31;
   const unsigned per_cta32 = (unsigned)a.per_cta;
-  const unsigned lane_lt = (1u << lane) - 1u;
   unsigned* const my_queue = a.queue + (size_t)blockIdx.x * a.per_cta;
   uint2* const my_cq = a.cqueue + (size_t)blockIdx.x * a.per_cta * 6;   // <= 2n first-level records + <= 2 per live record (S1d)
   const float height_bg = (float)g.height_bg;

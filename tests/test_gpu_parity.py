@@ -571,14 +571,15 @@ def test_fused_rewrites_every_bev_byte(pkg, synth):
     pr.close()
 
 
-@pytest.mark.parametrize("sensor,frames_per_sm", [("vls128", 6), ("hdl64", 7)])
-def test_fused_store_warp_never_skips_a_frame(pkg, synth, sensor, frames_per_sm):
+@pytest.mark.parametrize("sensor,res,frames_per_sm", [("vls128", 0.2, 6), ("hdl64", 0.2, 7), ("hdl32", 0.1, 6)])
+def test_fused_store_warp_never_skips_a_frame(pkg, synth, sensor, res, frames_per_sm):
     """Six or seven sweeps per CTA with a long point pass and the small (0.2 m) image: the store warp is
     done with a frame's zero lines long before the compute warps reach the next frame's BEV phase.  It
     must then wait for that frame's block cursor to be reset (a stale cursor reads "no blocks left" and
     the frame's zero lines would never be written; with fewer than five frames per CTA the CTA's last two
-    frames, written by all warps at the end, hide it).  Outputs start as NaN; every frame is compared on
-    the device with the generic path's result for the same sweep."""
+    frames, written by all warps at the end, hide it).  The third case is the opposite regime: a short point
+    pass and a four times larger image, so the compute warps wait for the store warp instead.  Outputs start
+    as NaN; every frame is compared on the device with the generic path's result for the same sweep."""
     import torch
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     distinct = 8
@@ -586,9 +587,9 @@ def test_fused_store_warp_never_skips_a_frame(pkg, synth, sensor, frames_per_sm)
     sweeps = [synth.make_sweep(sensor, seed=7000 + i, near_heavy=(sensor == "vls128")) for i in range(distinct)]
     n_pts = len(sweeps[0])
     base = torch.from_numpy(np.concatenate(sweeps)).cuda()
-    ref = _device_batch(pkg, base, distinct, n_pts, 1, (0.2, 0.2))
+    ref = _device_batch(pkg, base, distinct, n_pts, 1, (res, res))
     d = base.repeat(n_frames // distinct, 1)
-    pr = pkg.LidarProjector(device=0, path=2, firing_stride=synth.SENSORS[sensor][0])
+    pr = pkg.LidarProjector(device=0, path=2, bev_res=(res, res), firing_stride=synth.SENSORS[sensor][0])
     for rep in range(2):
         out = pr.alloc_outputs(n_frames, winner=True)
         out["bev"].fill_(float("nan"))
@@ -598,9 +599,10 @@ def test_fused_store_warp_never_skips_a_frame(pkg, synth, sensor, frames_per_sm)
         assert pr.last_path == "fused"
         for k in ("bev", "range", "winner"):
             got = out[k].view((n_frames // distinct, distinct) + tuple(out[k].shape[1:]))
-            same = (got == ref[k][None]).flatten(2).all(dim=2)
+            same = torch.stack([(got[:, j] == ref[k][j]).flatten(1).all(dim=1) for j in range(distinct)], dim=1)
             assert bool(same.all()), "%s: frames %s differ" % (k, torch.nonzero(~same.flatten())[:16].flatten().tolist())
         del out
+        torch.cuda.empty_cache()
     pr.close()
 
 

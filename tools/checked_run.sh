@@ -10,7 +10,7 @@ cd "$(dirname "$0")/.."
 if [ "$1" = build ]; then
   cd sensor-fusion-pose-estimation-challenge_b200/csrc && make -j4 > /dev/null && mkdir -p ../../gpurun_variants &&
   nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-Wall,-fvisibility=hidden -DSFPE_CHECKED -c sfpe_fused.cu -o /tmp/fused_chk.o &&
-  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../../gpurun_variants/checked.so sfpe_api.o sfpe_generic.o /tmp/fused_chk.o sfpe_colormap.o sfpe_post.o sfpe_transport.o -lpthread && echo built
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../../gpurun_variants/checked.so sfpe_api.o sfpe_generic.o /tmp/fused_chk.o sfpe_colormap.o sfpe_post.o sfpe_transport.o sfpe_static.o sfpe_ext.o -lpthread && echo built
   exit $?
 fi
 TAG=${1:-r02}
