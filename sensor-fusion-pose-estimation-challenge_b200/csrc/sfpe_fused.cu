@@ -103,21 +103,25 @@ __device__ __forceinline__ void note_collision(uint2* __restrict__ cq, unsigned*
   }
 }
 
-// the same for the four points of a point-pass step: one reservation per thread
+// the same for the four points of a point-pass step: one reservation per thread.  The caller passes key 0 for a
+// point without a cell (old = EMPTY then): EMPTY ^ key has bucket bits set for key 0 and for every real key (its
+// bucket is <= 16381 < 0x3FFF), so "equal bucket" is one XOR and one compare per point, and everything else
+// happens only for the few points that did meet an equal-bucket key.
 __device__ __forceinline__ void note_collisions4(uint2* __restrict__ cq, unsigned* misc, const int (&cell)[4],
                                                  const unsigned (&key)[4], const unsigned (&old)[4], unsigned cap) {
-  unsigned nrec = 0u, hit = 0u;
+  const bool c0 = (old[0] ^ key[0]) < (1u << IDX_BITS32), c1 = (old[1] ^ key[1]) < (1u << IDX_BITS32);
+  const bool c2 = (old[2] ^ key[2]) < (1u << IDX_BITS32), c3 = (old[3] ^ key[3]) < (1u << IDX_BITS32);
+  if (c0 | c1 | c2 | c3) {
+    const bool c[4] = {c0, c1, c2, c3};
+    unsigned nrec = 0u;
 #pragma unroll
-  for (int u = 0; u < 4; ++u) {
-    const bool c = old[u] != KEY32_EMPTY && ((old[u] ^ key[u]) >> IDX_BITS32) == 0;
-    if (c) { hit |= 1u << u; nrec += key[u] < old[u] ? 2u : 1u; }
-  }
-  if (hit) {
+    for (int u = 0; u < 4; ++u)
+      if (c[u]) nrec += key[u] < old[u] ? 2u : 1u;
     unsigned pos = atomicAdd(&misc[7], nrec);
     CHK(pos + nrec <= cap);
 #pragma unroll
     for (int u = 0; u < 4; ++u)
-      if (hit & (1u << u)) {
+      if (c[u]) {
         cq[pos++] = make_uint2((unsigned)cell[u], key[u] & IDX_MASK32);
         if (key[u] < old[u]) cq[pos++] = make_uint2((unsigned)cell[u], old[u] & IDX_MASK32);
       }
@@ -588,7 +592,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
           key[u] = ((unsigned)ifl << IDX_BITS32) | (unsigned)i;
         }
         defer[u] = valid && (undecided || !okr);
-        if (!valid || defer[u] || !g.enable_range) cell[u] = -1;
+        if (!valid || defer[u] || !g.enable_range) { cell[u] = -1; key[u] = 0u; }   // (key 0: see note_collisions4)
         if (defer[u]) bb[u] = NO_BUCKET;
       }
       if (defer[0] | defer[1] | defer[2] | defer[3]) {   // rare: one reservation per thread
