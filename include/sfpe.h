@@ -87,7 +87,9 @@ typedef struct {
   double bev_res_y;    /* res[0]: step of the y bin edges */
   int32_t enable_range; /* compute the range scan */
   int32_t enable_bev;   /* compute the BEV density */
-  /* extensions, default off (parity unpinned) */
+  /* extensions, default off (parity unpinned: no reference code).  Both run with the fused
+   * kernel when the batch qualifies for it (packed float32 points, float32 outputs): the extrinsic inside it, the
+   * slices in kernels of their own after it (sfpe_last_path "fused+ext"); otherwise on the generic path. */
   int32_t use_extrinsic; /* apply p' = float32(M[3x4] * (x,y,z,1)) before projecting */
   int32_t n_slices;      /* >0: MV3D height-slice maps + intensity-of-highest-point */
   double extrinsic[12];
