@@ -146,20 +146,21 @@ __device__ __forceinline__ float4 xf_point(const DevGrid& g, float4 v) {
 // several candidates are in flight together); reloaded only when the holder changes under us.
 template <bool XF>
 __device__ __forceinline__ void settle_candidate(const DevGrid& g, const float4* __restrict__ frame_pts, unsigned* addr,
-                                                 const float4 v, unsigned idx, unsigned cur, float4 hv) {
-  const double rho = rho_of_f4(v);
+                                                 const double rho, unsigned idx, unsigned cur, double hrho) {
+  // rho: the candidate's range, hrho: the range of the holder `cur` (both computed by the caller, all candidates of
+  // a round together, so that the fp64 square roots overlap); recomputed only when the holder changes under us
   const unsigned my_key = (quant_rho(rho) << IDX_BITS32) | idx;
   for (;;) {
     if (cur == my_key) return;
     if ((cur >> IDX_BITS32) < (my_key >> IDX_BITS32)) return;      // a nearer bucket holds the cell
     if ((cur >> IDX_BITS32) == (my_key >> IDX_BITS32)) {
       const unsigned ci = cur & IDX_MASK32;
-      if (better(rho_of_f4(hv), ci, rho, idx)) return;
+      if (better(hrho, ci, rho, idx)) return;
     }
     const unsigned seen = atomicCAS(addr, cur, my_key);
     if (seen == cur) return;
     cur = seen;
-    hv = xf_point<XF>(g, __ldg(frame_pts + (cur & IDX_MASK32)));
+    hrho = rho_of_f4(xf_point<XF>(g, __ldg(frame_pts + (cur & IDX_MASK32))));
   }
 }
 
@@ -718,9 +719,15 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
               if (act[u] && pv[u].x + hv[u].y == 1.2345f) keys[0] = 0u;
             continue;
           }
+          double pr[4], hr[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {   // eight independent square roots
+            pr[u] = act[u] ? rho_of_f4(pv[u]) : 0.0;
+            hr[u] = act[u] ? rho_of_f4(hv[u]) : 0.0;
+          }
 #pragma unroll
           for (int u = 0; u < 4; ++u)
-            if (act[u]) settle_candidate<XF>(g, fp, keys + en[u].x, pv[u], en[u].y, cur[u], hv[u]);
+            if (act[u]) settle_candidate<XF>(g, fp, keys + en[u].x, pr[u], en[u].y, cur[u], hr[u]);
         }
       }
       compute_sync();
