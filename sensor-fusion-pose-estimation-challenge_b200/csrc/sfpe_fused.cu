@@ -215,7 +215,7 @@ constexpr int CT = FUSED_THREADS - 32 * STORE_WARPS;   // 480 compute threads
 constexpr int CW = CT / 32;                            // 15 compute warps
 constexpr int MAX_BUCKETS = 64;                        // BEV entry buckets (consecutive tiles share one beyond 64 tiles)
 constexpr int NO_BUCKET = 255;
-constexpr long long FILL_IN_IV = 192, FILL_OUT_IV = 384;   // store-warp pacing, cycles per 8 KB group
+constexpr long long FILL_IN_IV = 128, FILL_OUT_IV = 256;   // store-warp pacing, cycles per 8 KB group
 constexpr int ROW_CELLS = 256;                         // one output row of the store warp: 32 lanes x 32 bytes = 1 KB
 constexpr int GROUP_ROWS = 8;                          // rows per claimed group (8 KB)
 
@@ -521,21 +521,27 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     compute_sync();
     PROF_STAMP(0);
 
-    auto load4 = [&](float4 (&v)[4], int q) {
+    // (x, y, z only: the intensity is not looked at before the resolve, and three registers per point instead of
+    // four leave room in the two register sets of the software pipeline)
+    auto ld3 = [&](const float4* p) {
+      const float2 xy = __ldg(reinterpret_cast<const float2*>(p));
+      return make_float3(xy.x, xy.y, __ldg(reinterpret_cast<const float*>(p) + 2));
+    };
+    auto load4 = [&](float3 (&v)[4], int q) {
       const int i0 = step_base(q) + lane;
       const float4* const p0 = fp + i0;
       if (i0 - lane + 3 * fstride + 32 <= n32) {   // the whole step lies inside the frame (warp-uniform): no bounds checks
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = __ldg(p0 + u * fstride);
+        for (int u = 0; u < 4; ++u) v[u] = ld3(p0 + u * fstride);
       } else {
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const int i = i0 + u * fstride;
-          v[u] = i < n32 ? __ldg(fp + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+          v[u] = i < n32 ? ld3(fp + i) : make_float3(0.f, 0.f, 0.f);
         }
       }
     };
-    auto rasterise4 = [&](const float4 (&v)[4], const int q) {
+    auto rasterise4 = [&](const float3 (&v)[4], const int q) {
       if (!DBG(64)) prefetch_step(q + 3 * CW);   // L2 prefetch three steps ahead
       const int i0 = step_base(q) + lane;
       // Per point, branch-free (so that the four points of a thread interleave): every decision
@@ -550,7 +556,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       for (int u = 0; u < 4; ++u) {
         const int i = i0 + u * fstride;
         const bool valid = i < n32;
-        const float4 w = xf_point<XF>(g, v[u]);
+        const float4 w = xf_point<XF>(g, make_float4(v[u].x, v[u].y, v[u].z, 0.f));
         const float x = w.x, y = w.y, z = w.z;
         bool undecided = false;
         be[u] = 0u; bb[u] = NO_BUCKET; cell[u] = -1; key[u] = 0u;
@@ -635,7 +641,7 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       note_collisions4(my_cq, misc, cell, key, old, 6u * per_cta32);
     };
     {
-      float4 va[4], vb[4];
+      float3 va[4], vb[4];
       int q = tid >> 5;
       load4(va, q);
       while (q < n_steps) {
