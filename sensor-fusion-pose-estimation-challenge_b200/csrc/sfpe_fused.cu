@@ -333,9 +333,9 @@ __device__ __forceinline__ void lut8(const float* lut, const uint2 e, float4& v0
 // window and every SM -- they run in step -- saturates HBM with zeros while the point loads
 // starve; measured optimum, profiles/README.md.)
 template <bool XF>   // one copy per kernel instantiation (a copy shared by two kernels was assembled wrongly: see __graft_entry__.check_sass)
-__device__ __noinline__ void bev_write_frame(const BevJob& job, unsigned* cursor, unsigned* misc, const int lane,
+__device__ __noinline__ void bev_write_frame(const BevJob job, unsigned* cursor, unsigned* misc, const int lane,
                                              const bool paced) {
-  const BevJob j = job;   // in registers (the caller's copy lives in local memory)
+  const BevJob j = job;   // (by value: in registers, no stack frame)
   const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
   const int myline = lane >> 2;
   // claim the next block (-1: none left) and load its line bitmaps (lane i < 8: rows 4i..4i+3 of the
