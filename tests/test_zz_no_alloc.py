@@ -111,7 +111,7 @@ def test_static_range_scan_matches_project_batch_on_calls_in_a_row():
     for _ in range(3):
         assert _static_call(lib_mod, params, c["pts"], c["n"], c["offs"], c["max_n"], 0, got, c["layout"], stream) == 0
     torch.cuda.synchronize()
-    assert torch.cuda.mem_get_info(0)[0] == before
+    assert abs(torch.cuda.mem_get_info(0)[0] - before) < (2 << 20)   # device allocations come in 2 MiB steps
 
 
 def test_static_range_scan_refuses_grids_beyond_its_array():
