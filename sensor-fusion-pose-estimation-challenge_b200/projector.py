@@ -86,6 +86,8 @@ class LidarProjector:
 
     @property
     def last_path(self):
+        """Code path of the last project(): "fused", "fused+ext" (fused kernel + the height-slice / intensity
+        kernels of the extension) or "generic"."""
         return self.lib.sfpe_last_path(self._ctx).decode()
 
     PHASES = ("key_init", "point_pass", "deferred_fp64", "range_resolve", "bev_compose", "bev_redo", "bev_line_write", "settle",
