@@ -353,7 +353,8 @@ def run_ours(a):
             "points_per_s": value * a.n_pts,
             "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": total_ms / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32 decisions proven by guard bands, f64 where unproven (bit-exact with the reference's f64); f32 outputs",
+            "dtype": "f32",
+            "dtype_note": "f32 decisions proven by guard bands, f64 where unproven (bit-exact with the reference's f64); f32 outputs",
             "data": "synthetic", "config": workload_config(a),
             "path": path_timed, "gpu_launches": int(launches), "frames_with_status": status_bad, "dropped_mean": dropped_mean,
             "verified_frames": verified,
