@@ -914,11 +914,23 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
       unsigned* const bm_k = a.rowbits + ((size_t)blockIdx.x * 2 + par) * (a.rows_cap >> 2);   // one byte per row
       unsigned char* const lf = reinterpret_cast<unsigned char*>(tile + tw);   // line flags of the tile: byte (cell >> 5)
       const int lbw = T >> 7;                  // words of the line flags (8 bytes per row)
+      // The parking area and the block cursor of this frame parity are free once frame k-2 is written.  If the
+      // store warp is not there yet, the compute warps do not wait for it: they claim blocks of frame k-2 from the
+      // same cursor and write them (as all warps do for a CTA's last frames) -- sixteen warps instead of one.
+      if (store_active && frames_done >= 2u) {
+        if ((int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) {   // (one shared-memory read per warp: uniform)
+          if (tid == 0) misc[11] = 2u;   // unpaced
+          const unsigned k2 = frames_done - 2u;
+          const int fk = (int)*reinterpret_cast<volatile unsigned*>(&misc[12 + (k2 & 3u)]) - 1;
+          const BevJob j2 = make_bev_job(a, cells, fk, k2, *reinterpret_cast<volatile unsigned*>(&misc[104 + (k2 & 3u)]));
+          bev_write_frame<XF>(j2, &misc[108 + (k2 & 1u)], misc, lane, false);
+        }
+        compute_sync();   // nobody claims from the cursor any more (the store warp finds it exhausted)
+      }
       if (tid == 0) {
         misc[11] = 1u;   // compose works in shared memory: store-warp window open
-        // the parking area of this frame parity is free once the store warp has written frame k-2
         if (store_active && frames_done >= 2u && (int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) {
-          misc[11] = 2u;   // we wait for the store warp: unpaced
+          misc[11] = 2u;   // the store warp is finishing its last blocks of frame k-2
           while ((int)(ld_acquire_smem(&misc[4]) - (frames_done - 1u)) < 0) __nanosleep(200);
           misc[11] = 1u;
         }
