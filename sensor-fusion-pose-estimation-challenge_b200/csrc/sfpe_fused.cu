@@ -323,15 +323,15 @@ __device__ __forceinline__ void lut8(const float* lut, const uint2 e, float4& v0
   v1 = lut4(lut, e.y);
 }
 // A writer claims blocks of 32 rows from `cursor` (one claimer in the steady state: the store warp;
-// all warps for a CTA's last frame); the line bitmaps of the block after next are in flight while
+// all warps for a CTA's last frames, and the compute warps when they would otherwise wait for the
+// store warp at the start of a BEV phase); the line bitmaps of the block after next are in flight while
 // the current block is written, 8 rows (8 KB) at a time.  A block is claimed once its tiles are
 // parked (misc[5]).
-// paced: one group per FILL_IN_IV cycles (25.6 B/clk) while misc[11] says that the compute warps
-// are in a phase that hardly uses the SM's path to L2 (point pass, BEV compose: registers and
-// shared memory, no waiting on loads), per FILL_OUT_IV (5.3 B/clk) while they move data
-// themselves or wait on loads, unpaced when they wait for the store warp.  (Faster inside the
-// window and every SM -- they run in step -- saturates HBM with zeros while the point loads
-// starve; measured optimum, profiles/README.md.)
+// paced: at most one group per FILL_IN_IV cycles while misc[11] says that the compute warps are in
+// a phase that hardly uses the SM's path to L2 (point pass, BEV compose: registers and shared
+// memory, no waiting on loads), per FILL_OUT_IV while they move data themselves or wait on loads,
+// unpaced when they wait for the store warp.  (The optimum is flat: 128..192 / 256..384 within
+// +-0.5 %, and one warp does not move more than ~8-14 B/clk unpaced either; profiles/README.md.)
 template <bool XF>   // one copy per kernel instantiation (a copy shared by two kernels was assembled wrongly: see __graft_entry__.check_sass)
 __device__ __noinline__ void bev_write_frame(const BevJob job, unsigned* cursor, unsigned* misc, const int lane,
                                              const bool paced) {
@@ -503,8 +503,8 @@ k_fused_sweep(const __grid_constant__ DevGrid g, const __grid_constant__ FusedAr
     // beams: lane = beam, and a thread's four points are the same beam at four consecutive azimuths
     // (a.spw_log2: beams per firing = 32 << spw_log2, a hint -- any value rasterises any cloud
     // correctly).  Such neighbours mostly fall into the same BEV cell and almost always into the same
-    // BEV tile, so a thread merges them into runs (cell, count) and the warp appends all its runs
-    // with ONE match / shared-memory atomic.  The points of the next step are loaded while the
+    // BEV tile, so a thread merges them into runs (cell, count); every run is appended to its tile's
+    // bucket with one shared-memory atomic.  The points of the next step are loaded while the
     // current ones are rasterised, into the other of two register sets (no copies).
     const int n32 = (int)n;
     const int spw_log2 = a.spw_log2, fstride = 32 << spw_log2;          // points per firing
