@@ -85,6 +85,18 @@ def test_static_entry_validates_before_touching_cuda():
     assert "#define SFPE_STATIC_MAX_CELLS (1 << 18)" in src and lib_mod.STATIC_MAX_CELLS == 1 << 18
 
 
+def test_fused_kernels_keep_their_32_byte_stores():
+    """Build-time SASS check (see __graft_entry__.check_sass): every instantiation of k_fused_sweep holds the same
+    STG.256 stores.  nvcc 12.9 once assembled 60 of 63 of them as 4-byte stores in one of two kernels."""
+    import shutil
+    import __graft_entry__ as ge
+    csrc = os.path.join(ROOT, "sensor-fusion-pose-estimation-challenge_b200", "csrc")
+    if not os.path.isfile(os.path.join(csrc, "sfpe_fused.o")) or shutil.which("cuobjdump") is None:
+        pytest.skip("no object file / cuobjdump here (the library was built elsewhere)")
+    counts = ge.check_sass(csrc)
+    assert len(counts) == 2 and len(set(counts.values())) == 1
+
+
 def test_no_cpu_fallback_without_gpu():
     import torch
     if torch.cuda.is_available():
